@@ -1,0 +1,215 @@
+/*
+ * b200_abi.h — C-ABI of libb200ops.so: the B200 (sm_100a) replacement for the
+ * GPU operators on micro-vllm's paged-KV attention hot path.
+ *
+ * Every entry point below is what the reference's Python operator modules bind
+ * instead of flash-attn / Triton.  Each declaration cites the reference
+ * interface it replaces (paths relative to the reference repo root).
+ *
+ * Conventions:
+ *   - plain pointers and sizes only; device pointers come from tensor.data_ptr()
+ *   - strides are in ELEMENTS, innermost (head_dim / hidden) stride must be 1
+ *   - activations / caches / rotary tables are bf16, indices are int32,
+ *     workspaces are fp32
+ *   - `stream` is a cudaStream_t passed as void* (torch.cuda.current_stream().cuda_stream)
+ *   - return value: 0 = OK, <0 = argument error (B200_E_*), >0 = cudaError_t
+ *   - no entry point allocates, synchronises or touches host memory after
+ *     argument validation, so all of them are CUDA-graph capturable
+ */
+#ifndef B200_ABI_H
+#define B200_ABI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 3
+
+/* argument errors */
+#define B200_E_NULL        (-1)  /* required pointer is NULL            */
+#define B200_E_SHAPE       (-2)  /* unsupported shape (head_dim, group) */
+#define B200_E_ALIGN       (-3)  /* pointer / stride not 16-byte aligned */
+#define B200_E_RANGE       (-4)  /* value out of range                  */
+#define B200_E_UNSUPPORTED (-5)  /* feature not implemented             */
+
+/* weight dtype selector for the norm kernels */
+#define B200_DT_BF16 0
+#define B200_DT_F32  1
+
+int b200_version(void);
+
+/* Human-readable description of the most recent non-zero return on this thread. */
+const char* b200_last_error(void);
+
+/* Number of SMs of the current device (used by the host-side split heuristic). */
+int b200_sm_count(void);
+
+/* ------------------------------------------------------------------------ *
+ * SwiGLU  — replaces kernel/swiglu.py:6-46 (_swiglu_kernel), launched from
+ * swiglu_fused (:49-93) and swiglu_gemm (:100-148).
+ *   out[r, c] = bf16( silu(f32(gate_up[r, d + c])) * f32(gate_up[r, c]) )
+ * gate_up is [rows, 2*d] (up = first half, gate = second half), out [rows, d].
+ * ------------------------------------------------------------------------ */
+int b200_swiglu(const void* gate_up, void* out,
+                int64_t rows, int64_t d,
+                int64_t stride_in, int64_t stride_out,
+                void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * RMSNorm — replaces kernel/rmsnorm_add.py:9-34 (_rmsnorm_kernel) and
+ * :133-167 (_rmsnorm_gemm_kernel); wrappers rmsnorm (:37-53), rmsnorm_ (:170-206).
+ *   y = bf16( f32(x) * rsqrt(mean(f32(x)^2) + eps) * f32(w) )
+ * ------------------------------------------------------------------------ */
+int b200_rmsnorm(const void* x, const void* w, void* y,
+                 int64_t rows, int64_t n,
+                 int64_t stride_x, int64_t stride_y,
+                 float eps, int w_dtype,
+                 void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Residual-add + RMSNorm — replaces kernel/rmsnorm_add.py:56-86,
+ * kernel/rmsnorm_residual.py:11-41 and :74-124; wrappers
+ * rmsnorm_residual_fused / _gemm / _hybrid.
+ *   s = f32(x) + f32(r); res_out = bf16(s); rrms = rsqrt(mean(s^2) + eps)
+ *   y = bf16( f32(res_out) * rrms * f32(w) )      (second pass re-reads the
+ *   ROUNDED residual, rmsnorm_residual.py:119)
+ * ------------------------------------------------------------------------ */
+int b200_rmsnorm_residual(const void* x, const void* r, const void* w,
+                          void* y, void* res_out,
+                          int64_t rows, int64_t n,
+                          int64_t stride_x, int64_t stride_r,
+                          int64_t stride_y, int64_t stride_res,
+                          float eps, int w_dtype,
+                          void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * store_kvcache — replaces core/cache_manager.py:74-140 (store_kvcache_kernel),
+ * launched from store_kvcache (:143-194) / store_kvcache_batch (:196-255).
+ *   cache[slot / block_size, slot % block_size, h, :] = key/value[t, h, :]
+ *   for every token t with slot_mapping[t] != -1   (bit-exact copy)
+ * key/value [T, H, D] with element strides (kt, kh) / (vt, vh), D contiguous;
+ * caches [n_blocks, block_size, H, D] with element strides (cb, cs, ch).
+ * ------------------------------------------------------------------------ */
+int b200_store_kvcache(const void* key, const void* value,
+                       void* k_cache, void* v_cache,
+                       const int32_t* slot_mapping,
+                       int64_t T, int64_t H, int64_t D,
+                       int64_t kt, int64_t kh, int64_t vt, int64_t vh,
+                       int64_t n_blocks, int64_t block_size,
+                       int64_t cb, int64_t cs, int64_t ch,
+                       void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Paged decode attention — replaces the flash_attn_with_kvcache call at
+ * core/layer/model_graph.py:161-168 and core/paged_attention.py:281-293
+ * (seqlen_q == 1).  One launch does, for every batch row b:
+ *   pos = cache_seqlens[b]
+ *   q,k_new rotated at cos/sin[pos] (NeoX halves or interleaved pairs),
+ *   rotated k_new and raw v_new written to page block_table[b, pos/bs],
+ *   slot pos % bs,
+ *   out[b] = softmax(scale * q . K[0..pos]^T) . V[0..pos]     (split-KV,
+ *   fp32 online softmax, partials merged by the last-arriving CTA).
+ * k_new/v_new may be NULL (no append, no rotary, attends over [0, pos)).
+ * cos/sin may be NULL (no rotary).
+ *
+ * Workspace (caller-owned, sized by b200_decode_workspace_bytes, zeroed ONCE
+ * by the caller before first use; the kernel leaves it reusable):
+ *   [ counters | lse partials | O partials ]
+ * ------------------------------------------------------------------------ */
+typedef struct b200_decode_args {
+    const void* q;            /* [B, Hq, D] bf16                                  */
+    const void* k_new;        /* [B, Hkv, D] bf16 or NULL                         */
+    const void* v_new;        /* [B, Hkv, D] bf16 or NULL                         */
+    void*       k_cache;      /* [n_blocks, block_size, Hkv, D] bf16              */
+    void*       v_cache;
+    const void* rotary_cos;   /* [rot_rows, rotary_dim/2] bf16 or NULL            */
+    const void* rotary_sin;
+    const int32_t* cache_seqlens; /* [B]                                          */
+    const int32_t* block_table;   /* [B, max_blocks_per_seq]                      */
+    void*       out;          /* [B, Hq, D] bf16                                  */
+    float*      softmax_lse;  /* optional [B, Hq] fp32 (natural log) or NULL      */
+    void*       workspace;    /* see b200_decode_workspace_bytes                  */
+    int64_t     workspace_bytes;
+    int32_t B, Hq, Hkv, D;
+    int32_t rotary_dim;       /* 0 = no rotary; multiple of 16, <= D              */
+    int32_t rotary_interleaved; /* 0 = NeoX halves (model_graph.py:166), 1 = GPT-J pairs (flash-attn default, paged_attention.py:281) */
+    int32_t rot_rows;         /* rows in the cos/sin tables                       */
+    int32_t n_blocks, block_size, max_blocks_per_seq;
+    int64_t q_stride_b, q_stride_h;
+    int64_t k_stride_b, k_stride_h;
+    int64_t v_stride_b, v_stride_h;
+    int64_t o_stride_b, o_stride_h;
+    int64_t kc_stride_blk, kc_stride_tok, kc_stride_h;   /* k_cache strides */
+    int64_t vc_stride_blk, vc_stride_tok, vc_stride_h;   /* v_cache strides */
+    int64_t bt_stride_b;      /* block_table row stride                           */
+    int32_t num_splits;       /* >= 1; grid is (num_splits, Hkv*groups, B)        */
+    int32_t variant;          /* tuning variant, 0 = default                      */
+    float   softmax_scale;
+} b200_decode_args;
+
+int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                                    int32_t num_splits);
+
+int b200_paged_attn_decode(const b200_decode_args* args, void* stream);
+
+/* Stand-alone LSE combine of split partials laid out as in the decode
+ * workspace: o_part [B, Hq, S, D] fp32 (already normalised per split),
+ * lse_part [B, Hq, S] fp32 (natural log, -inf = empty split).  The decode
+ * entry point fuses this step; it is exported for callers that produce
+ * partials themselves (flash-attn's combine kernel equivalent). */
+int b200_lse_combine(const float* o_part, const float* lse_part,
+                     void* out, float* lse_out,
+                     int32_t B, int32_t Hq, int32_t S, int32_t D,
+                     int64_t o_stride_b, int64_t o_stride_h,
+                     void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Paged prefill attention — replaces RoPE.forward (core/layer/rope.py:10-39)
+ * + the flash_attn_with_kvcache call at core/layer/model_prefill.py:49-52.
+ * For every batch row b with S new tokens on top of P_b = cache_seqlens[b]
+ * cached tokens:
+ *   1. q, k rotated at positions P_b + i (or raw when cos == NULL: the
+ *      reference pre-rotates with RoPE.forward),
+ *   2. K (rotated) and V scattered into pages through block_table,
+ *   3. causal (bottom-right aligned) attention of the S queries over
+ *      positions [0, P_b + S) read back from the pages, on tcgen05/TMEM.
+ * ------------------------------------------------------------------------ */
+typedef struct b200_prefill_args {
+    const void* q;            /* [B, S, Hq, D] bf16  */
+    const void* k;            /* [B, S, Hkv, D] bf16 */
+    const void* v;            /* [B, S, Hkv, D] bf16 */
+    void*       k_cache;
+    void*       v_cache;
+    const void* rotary_cos;   /* optional */
+    const void* rotary_sin;
+    const int32_t* cache_seqlens; /* [B] prefix lengths P_b                 */
+    const int32_t* block_table;   /* [B, max_blocks_per_seq]                */
+    void*       out;          /* [B, S, Hq, D] bf16 */
+    void*       workspace;    /* b200_prefill_workspace_bytes: rotated Q    */
+    int64_t     workspace_bytes;
+    int32_t B, S, Hq, Hkv, D;
+    int32_t rotary_dim, rotary_interleaved, rot_rows;
+    int32_t n_blocks, block_size, max_blocks_per_seq;
+    int32_t max_prefix;       /* upper bound on cache_seqlens[b] (grid sizing; table capacity if unknown) */
+    int32_t causal;
+    int64_t q_stride_b, q_stride_s, q_stride_h;
+    int64_t k_stride_b, k_stride_s, k_stride_h;
+    int64_t v_stride_b, v_stride_s, v_stride_h;
+    int64_t o_stride_b, o_stride_s, o_stride_h;
+    int64_t kc_stride_blk, kc_stride_tok, kc_stride_h;
+    int64_t vc_stride_blk, vc_stride_tok, vc_stride_h;
+    int64_t bt_stride_b;
+    int32_t variant;
+    float   softmax_scale;
+} b200_prefill_args;
+
+int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D);
+
+int b200_paged_attn_prefill(const b200_prefill_args* args, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_ABI_H */

@@ -1,0 +1,268 @@
+"""b200ops — thin torch-tensor front end over the libb200ops C-ABI.
+
+Tensors are only used for their device pointers, shapes and strides; every
+function launches on torch's *current* CUDA stream, allocates nothing unless
+stated, and never synchronises, so all of them can be captured in a CUDA graph
+(reference contract: core/layer/model_graph.py:240-250).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # noqa: F401
+
+__all__ = [
+    "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
+    "paged_attn_prefill", "lse_combine", "decode_num_splits", "B200Error", "LIB_PATH",
+]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _req_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise AssertionError("b200ops: all tensors must be CUDA tensors (no CPU fallback exists)")
+
+
+def _wdt(w: torch.Tensor) -> int:
+    if w.dtype == torch.bfloat16:
+        return _lib.DT_BF16
+    if w.dtype == torch.float32:
+        return _lib.DT_F32
+    raise AssertionError(f"b200ops: norm weight dtype {w.dtype} unsupported (bf16 / fp32)")
+
+
+# ------------------------------------------------------------------ elementwise
+def swiglu(gate_up: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """out[r, c] = silu(gate_up[r, d+c]) * gate_up[r, c]   (kernel/swiglu.py:18-46)."""
+    _req_cuda(gate_up, out)
+    assert gate_up.dtype == torch.bfloat16 and out.dtype == torch.bfloat16, "swiglu: bf16 only"
+    d2 = gate_up.shape[-1]
+    assert d2 % 2 == 0
+    d = d2 // 2
+    gu = gate_up.reshape(-1, d2)
+    o = out.view(-1, d)
+    assert gu.stride(1) == 1 and o.stride(1) == 1 and gu.shape[0] == o.shape[0]
+    check(lib.b200_swiglu(gu.data_ptr(), o.data_ptr(), gu.shape[0], d, gu.stride(0), o.stride(0), _stream()),
+          "b200_swiglu")
+    return out
+
+
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, out: torch.Tensor, eps: float) -> torch.Tensor:
+    _req_cuda(x, weight, out)
+    assert x.dtype == torch.bfloat16 and out.dtype == torch.bfloat16, "rmsnorm: bf16 activations only"
+    n = x.shape[-1]
+    x2, y2 = x.view(-1, n), out.view(-1, n)
+    assert x2.stride(1) == 1 and y2.stride(1) == 1 and weight.is_contiguous()
+    check(lib.b200_rmsnorm(x2.data_ptr(), weight.data_ptr(), y2.data_ptr(), x2.shape[0], n,
+                           x2.stride(0), y2.stride(0), float(eps), _wdt(weight), _stream()), "b200_rmsnorm")
+    return out
+
+
+def rmsnorm_residual(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                     out: torch.Tensor, res_out: torch.Tensor, eps: float):
+    _req_cuda(x, residual, weight, out, res_out)
+    for t in (x, residual, out, res_out):
+        assert t.dtype == torch.bfloat16, "rmsnorm_residual: bf16 activations only"
+    n = x.shape[-1]
+    x2, r2, y2, o2 = (t.view(-1, n) for t in (x, residual, out, res_out))
+    assert all(t.stride(1) == 1 for t in (x2, r2, y2, o2)) and weight.is_contiguous()
+    check(lib.b200_rmsnorm_residual(x2.data_ptr(), r2.data_ptr(), weight.data_ptr(), y2.data_ptr(), o2.data_ptr(),
+                                    x2.shape[0], n, x2.stride(0), r2.stride(0), y2.stride(0), o2.stride(0),
+                                    float(eps), _wdt(weight), _stream()), "b200_rmsnorm_residual")
+    return out, res_out
+
+
+def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                  slot_mapping: torch.Tensor, block_size: int) -> None:
+    _req_cuda(key, value, k_cache, v_cache, slot_mapping)
+    T, H, D = key.shape
+    assert key.dtype == value.dtype == k_cache.dtype == v_cache.dtype and key.element_size() == 2, \
+        "store_kvcache: 16-bit key/value/cache of one dtype"
+    assert slot_mapping.dtype == torch.int32 and slot_mapping.is_contiguous()
+    assert key.stride(2) == 1 and value.stride(2) == 1 and k_cache.stride(3) == 1 and v_cache.stride(3) == 1
+    assert k_cache.stride() == v_cache.stride() and k_cache.shape[1] == block_size
+    check(lib.b200_store_kvcache(key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                                 slot_mapping.data_ptr(), T, H, D,
+                                 key.stride(0), key.stride(1), value.stride(0), value.stride(1),
+                                 k_cache.shape[0], block_size,
+                                 k_cache.stride(0), k_cache.stride(1), k_cache.stride(2), _stream()),
+          "b200_store_kvcache")
+
+
+# ------------------------------------------------------------------ decode attention
+_SM_COUNT: dict[int, int] = {}
+_WORKSPACES: dict[tuple, torch.Tensor] = {}
+
+
+def sm_count(device: torch.device) -> int:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _SM_COUNT:
+        with torch.cuda.device(idx):
+            _SM_COUNT[idx] = max(1, lib.b200_sm_count())
+    return _SM_COUNT[idx]
+
+
+def decode_num_splits(batch: int, kv_heads: int, capacity_tokens: int, n_sm: int = 148,
+                      tokens_per_cta_chunk: int = 64, ctas_per_sm: int = 2, waves: int = 4) -> int:
+    """Split count from launch-time constants only (CUDA-graph capture fixes the grid;
+    model_graph.py:167 passes max(1, 32 // (4*bs)), which leaves 256 CTAs for 148 SMs at
+    bs=32).  Aim for `waves` full waves of CTAs; never more splits than the block table
+    could ever give work to."""
+    base = max(1, batch * kv_heads)
+    want = -(-n_sm * ctas_per_sm * waves // base)
+    cap = max(1, capacity_tokens // tokens_per_cta_chunk)
+    return int(max(1, min(want, cap, 128)))
+
+
+_RETIRED: list = []
+
+
+def _workspace(device: torch.device, nbytes: int, tag: str) -> torch.Tensor:
+    """Per (device, stream, operator) scratch.  Zero-filled once: the decode arrival
+    counters must start at 0 and the kernel resets them itself.  Outgrown buffers are
+    kept alive because captured CUDA graphs may still hold their addresses."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+    ws = _WORKSPACES.get(key)
+    if ws is None or ws.numel() < nbytes:
+        if ws is not None:
+            _RETIRED.append(ws)
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                      k_new: Optional[torch.Tensor], v_new: Optional[torch.Tensor],
+                      rotary_cos: Optional[torch.Tensor], rotary_sin: Optional[torch.Tensor],
+                      cache_seqlens: torch.Tensor, block_table: torch.Tensor,
+                      softmax_scale: Optional[float] = None, rotary_interleaved: bool = False,
+                      num_splits: int = 0, out: Optional[torch.Tensor] = None,
+                      softmax_lse: Optional[torch.Tensor] = None, variant: int = 0) -> torch.Tensor:
+    """q [B, Hq, D]; k_new/v_new [B, Hkv, D]; caches [n_blocks, block_size, Hkv, D];
+    returns out [B, Hq, D] (allocated unless given)."""
+    _req_cuda(q, k_cache, v_cache, k_new, v_new, rotary_cos, rotary_sin, cache_seqlens, block_table)
+    B, Hq, D = q.shape
+    n_blocks, block_size, Hkv, Dc = k_cache.shape
+    assert Dc == D and v_cache.shape == k_cache.shape
+    assert q.dtype == torch.bfloat16 and k_cache.dtype == torch.bfloat16 and v_cache.dtype == torch.bfloat16, \
+        "paged_attn_decode: bf16 only"
+    assert cache_seqlens.dtype == torch.int32 and block_table.dtype == torch.int32
+    assert cache_seqlens.is_contiguous() and cache_seqlens.shape[0] >= B
+    assert block_table.shape[0] >= B and block_table.stride(1) == 1
+    assert q.stride(2) == 1 and k_cache.stride(3) == 1 and v_cache.stride(3) == 1
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    assert out.stride(2) == 1
+    a = DecodeArgs()
+    a.q, a.k_cache, a.v_cache, a.out = q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), out.data_ptr()
+    if k_new is not None:
+        assert v_new is not None and k_new.shape == (B, Hkv, D) and v_new.shape == (B, Hkv, D)
+        assert k_new.dtype == torch.bfloat16 and v_new.dtype == torch.bfloat16
+        assert k_new.stride(2) == 1 and v_new.stride(2) == 1
+        a.k_new, a.v_new = k_new.data_ptr(), v_new.data_ptr()
+        a.k_stride_b, a.k_stride_h = k_new.stride(0), k_new.stride(1)
+        a.v_stride_b, a.v_stride_h = v_new.stride(0), v_new.stride(1)
+    if rotary_cos is not None:
+        assert rotary_sin is not None and rotary_cos.shape == rotary_sin.shape
+        assert rotary_cos.dtype == torch.bfloat16 and rotary_sin.dtype == torch.bfloat16
+        assert rotary_cos.is_contiguous() and rotary_sin.is_contiguous()
+        a.rotary_cos, a.rotary_sin = rotary_cos.data_ptr(), rotary_sin.data_ptr()
+        a.rot_rows, a.rotary_dim = rotary_cos.shape[0], 2 * rotary_cos.shape[1]
+    a.rotary_interleaved = 1 if rotary_interleaved else 0
+    a.cache_seqlens, a.block_table = cache_seqlens.data_ptr(), block_table.data_ptr()
+    if softmax_lse is not None:
+        assert softmax_lse.dtype == torch.float32 and softmax_lse.is_contiguous() and softmax_lse.numel() >= B * Hq
+        a.softmax_lse = softmax_lse.data_ptr()
+    a.B, a.Hq, a.Hkv, a.D = B, Hq, Hkv, D
+    a.n_blocks, a.block_size, a.max_blocks_per_seq = n_blocks, block_size, block_table.shape[1]
+    a.q_stride_b, a.q_stride_h = q.stride(0), q.stride(1)
+    a.o_stride_b, a.o_stride_h = out.stride(0), out.stride(1)
+    a.kc_stride_blk, a.kc_stride_tok, a.kc_stride_h = k_cache.stride(0), k_cache.stride(1), k_cache.stride(2)
+    a.vc_stride_blk, a.vc_stride_tok, a.vc_stride_h = v_cache.stride(0), v_cache.stride(1), v_cache.stride(2)
+    a.bt_stride_b = block_table.stride(0)
+    if num_splits <= 0:
+        num_splits = decode_num_splits(B, Hkv, block_table.shape[1] * block_size, sm_count(q.device))
+    a.num_splits, a.variant = int(num_splits), int(variant)
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 1.0 / math.sqrt(D)
+    if num_splits > 1:
+        need = lib.b200_decode_workspace_bytes(B, Hq, Hkv, D, num_splits)
+        ws = _workspace(q.device, need, "decode")
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+    check(lib.b200_paged_attn_decode(C.byref(a), _stream()), "b200_paged_attn_decode")
+    return out
+
+
+def lse_combine(o_part: torch.Tensor, lse_part: torch.Tensor, out: Optional[torch.Tensor] = None,
+                lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """o_part [B, Hq, S, D] fp32 (normalised per split), lse_part [B, Hq, S] fp32 -> out [B, Hq, D] bf16."""
+    _req_cuda(o_part, lse_part)
+    B, Hq, S, D = o_part.shape
+    assert o_part.dtype == torch.float32 and lse_part.dtype == torch.float32
+    assert o_part.is_contiguous() and lse_part.is_contiguous() and lse_part.shape == (B, Hq, S)
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=torch.bfloat16, device=o_part.device)
+    check(lib.b200_lse_combine(o_part.data_ptr(), lse_part.data_ptr(), out.data_ptr(),
+                               lse_out.data_ptr() if lse_out is not None else None,
+                               B, Hq, S, D, out.stride(0), out.stride(1), _stream()), "b200_lse_combine")
+    return out
+
+
+# ------------------------------------------------------------------ prefill attention
+def paged_attn_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
+                       k_cache: torch.Tensor, v_cache: torch.Tensor,
+                       rotary_cos: Optional[torch.Tensor], rotary_sin: Optional[torch.Tensor],
+                       cache_seqlens: torch.Tensor, block_table: torch.Tensor,
+                       softmax_scale: Optional[float] = None, causal: bool = True,
+                       rotary_interleaved: bool = False, max_prefix: Optional[int] = None,
+                       out: Optional[torch.Tensor] = None, variant: int = 0) -> torch.Tensor:
+    """q [B, S, Hq, D]; k, v [B, S, Hkv, D]; appends k/v at cache_seqlens[b] + i and attends
+    causally over [0, cache_seqlens[b] + S).  Returns out [B, S, Hq, D]."""
+    _req_cuda(q, k, v, k_cache, v_cache, rotary_cos, rotary_sin, cache_seqlens, block_table)
+    B, S, Hq, D = q.shape
+    n_blocks, block_size, Hkv, Dc = k_cache.shape
+    assert Dc == D and v_cache.shape == k_cache.shape and k.shape == (B, S, Hkv, D) and v.shape == k.shape
+    for t in (q, k, v, k_cache, v_cache):
+        assert t.dtype == torch.bfloat16, "paged_attn_prefill: bf16 only"
+        assert t.stride(-1) == 1
+    assert cache_seqlens.dtype == torch.int32 and block_table.dtype == torch.int32
+    assert cache_seqlens.is_contiguous() and block_table.stride(1) == 1
+    if out is None:
+        out = torch.empty((B, S, Hq, D), dtype=q.dtype, device=q.device)
+    a = PrefillArgs()
+    a.q, a.k, a.v, a.k_cache, a.v_cache, a.out = (t.data_ptr() for t in (q, k, v, k_cache, v_cache, out))
+    if rotary_cos is not None:
+        assert rotary_sin is not None and rotary_cos.shape == rotary_sin.shape
+        assert rotary_cos.dtype == torch.bfloat16 and rotary_cos.is_contiguous() and rotary_sin.is_contiguous()
+        a.rotary_cos, a.rotary_sin = rotary_cos.data_ptr(), rotary_sin.data_ptr()
+        a.rot_rows, a.rotary_dim = rotary_cos.shape[0], 2 * rotary_cos.shape[1]
+    a.rotary_interleaved = 1 if rotary_interleaved else 0
+    a.cache_seqlens, a.block_table = cache_seqlens.data_ptr(), block_table.data_ptr()
+    a.B, a.S, a.Hq, a.Hkv, a.D = B, S, Hq, Hkv, D
+    a.n_blocks, a.block_size, a.max_blocks_per_seq = n_blocks, block_size, block_table.shape[1]
+    cap = block_table.shape[1] * block_size
+    a.max_prefix = int(min(cap, max_prefix if max_prefix is not None else cap))
+    a.causal = 1 if causal else 0
+    a.q_stride_b, a.q_stride_s, a.q_stride_h = q.stride(0), q.stride(1), q.stride(2)
+    a.k_stride_b, a.k_stride_s, a.k_stride_h = k.stride(0), k.stride(1), k.stride(2)
+    a.v_stride_b, a.v_stride_s, a.v_stride_h = v.stride(0), v.stride(1), v.stride(2)
+    a.o_stride_b, a.o_stride_s, a.o_stride_h = out.stride(0), out.stride(1), out.stride(2)
+    a.kc_stride_blk, a.kc_stride_tok, a.kc_stride_h = k_cache.stride(0), k_cache.stride(1), k_cache.stride(2)
+    a.vc_stride_blk, a.vc_stride_tok, a.vc_stride_h = v_cache.stride(0), v_cache.stride(1), v_cache.stride(2)
+    a.bt_stride_b = block_table.stride(0)
+    a.variant = int(variant)
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 1.0 / math.sqrt(D)
+    need = lib.b200_prefill_workspace_bytes(B, S, Hq, D)
+    if need > 0:
+        ws = _workspace(q.device, need, "prefill")
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+    check(lib.b200_paged_attn_prefill(C.byref(a), _stream()), "b200_paged_attn_prefill")
+    return out

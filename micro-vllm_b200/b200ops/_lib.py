@@ -1,0 +1,115 @@
+"""ctypes binding of libb200ops.so (include/b200_abi.h).
+
+There is deliberately no fallback: if the shared library cannot be found or
+built, importing this module raises, and every operator in core/ and kernel/
+fails with it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+_i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
+
+E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
+DT_BF16, DT_F32 = 0, 1
+ABI_VERSION = 3
+
+
+class DecodeArgs(C.Structure):
+    """struct b200_decode_args (include/b200_abi.h)."""
+    _fields_ = [
+        ("q", _vp), ("k_new", _vp), ("v_new", _vp), ("k_cache", _vp), ("v_cache", _vp),
+        ("rotary_cos", _vp), ("rotary_sin", _vp), ("cache_seqlens", _vp), ("block_table", _vp),
+        ("out", _vp), ("softmax_lse", _vp), ("workspace", _vp), ("workspace_bytes", _i64),
+        ("B", _i32), ("Hq", _i32), ("Hkv", _i32), ("D", _i32),
+        ("rotary_dim", _i32), ("rotary_interleaved", _i32), ("rot_rows", _i32),
+        ("n_blocks", _i32), ("block_size", _i32), ("max_blocks_per_seq", _i32),
+        ("q_stride_b", _i64), ("q_stride_h", _i64),
+        ("k_stride_b", _i64), ("k_stride_h", _i64),
+        ("v_stride_b", _i64), ("v_stride_h", _i64),
+        ("o_stride_b", _i64), ("o_stride_h", _i64),
+        ("kc_stride_blk", _i64), ("kc_stride_tok", _i64), ("kc_stride_h", _i64),
+        ("vc_stride_blk", _i64), ("vc_stride_tok", _i64), ("vc_stride_h", _i64),
+        ("bt_stride_b", _i64),
+        ("num_splits", _i32), ("variant", _i32), ("softmax_scale", _f32),
+    ]
+
+
+class PrefillArgs(C.Structure):
+    """struct b200_prefill_args (include/b200_abi.h)."""
+    _fields_ = [
+        ("q", _vp), ("k", _vp), ("v", _vp), ("k_cache", _vp), ("v_cache", _vp),
+        ("rotary_cos", _vp), ("rotary_sin", _vp), ("cache_seqlens", _vp), ("block_table", _vp),
+        ("out", _vp), ("workspace", _vp), ("workspace_bytes", _i64),
+        ("B", _i32), ("S", _i32), ("Hq", _i32), ("Hkv", _i32), ("D", _i32),
+        ("rotary_dim", _i32), ("rotary_interleaved", _i32), ("rot_rows", _i32),
+        ("n_blocks", _i32), ("block_size", _i32), ("max_blocks_per_seq", _i32),
+        ("max_prefix", _i32), ("causal", _i32),
+        ("q_stride_b", _i64), ("q_stride_s", _i64), ("q_stride_h", _i64),
+        ("k_stride_b", _i64), ("k_stride_s", _i64), ("k_stride_h", _i64),
+        ("v_stride_b", _i64), ("v_stride_s", _i64), ("v_stride_h", _i64),
+        ("o_stride_b", _i64), ("o_stride_s", _i64), ("o_stride_h", _i64),
+        ("kc_stride_blk", _i64), ("kc_stride_tok", _i64), ("kc_stride_h", _i64),
+        ("vc_stride_blk", _i64), ("vc_stride_tok", _i64), ("vc_stride_h", _i64),
+        ("bt_stride_b", _i64),
+        ("variant", _i32), ("softmax_scale", _f32),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/b200_abi.h declares
+SIGNATURES = {
+    "b200_version": (C.c_int, []),
+    "b200_last_error": (C.c_char_p, []),
+    "b200_sm_count": (C.c_int, []),
+    "b200_swiglu": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "b200_rmsnorm": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _f32, C.c_int, _vp]),
+    "b200_rmsnorm_residual": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
+                                         _f32, C.c_int, _vp]),
+    "b200_store_kvcache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _i64,
+                                      _i64, _i64, _i64, _i64, _i64, _vp]),
+    "b200_decode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32, _i32]),
+    "b200_paged_attn_decode": (C.c_int, [C.POINTER(DecodeArgs), _vp]),
+    "b200_lse_combine": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp]),
+    "b200_prefill_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
+    "b200_paged_attn_prefill": (C.c_int, [C.POINTER(PrefillArgs), _vp]),
+}
+
+
+class B200Error(RuntimeError):
+    def __init__(self, code: int, where: str, msg: str):
+        kind = "argument error" if code < 0 else "cudaError"
+        super().__init__(f"{where}: {kind} {code}: {msg}")
+        self.code = code
+
+
+def _load() -> C.CDLL:
+    path = os.environ.get("B200OPS_LIB") or _build.LIB_PATH
+    if not os.path.exists(path) or (path == _build.LIB_PATH and not _build.is_fresh()):
+        try:
+            path = _build.build()
+        except Exception as e:   # noqa: BLE001 - re-raised as a hard import error
+            if not os.path.exists(path):
+                raise ImportError(
+                    f"libb200ops.so is missing and could not be built ({e}); "
+                    "the B200 operators have no fallback path") from e
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)      # AttributeError here = ABI mismatch, fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    ver = lib.b200_version()
+    if ver != ABI_VERSION:
+        raise ImportError(f"libb200ops.so ABI version {ver} != binding version {ABI_VERSION}; rebuild")
+    return lib
+
+
+lib = _load()
+LIB_PATH = lib._name
+
+
+def check(code: int, where: str) -> None:
+    if code != 0:
+        raise B200Error(code, where, lib.b200_last_error().decode(errors="replace"))

@@ -1,0 +1,218 @@
+"""Paged KV-cache allocator with device-resident int32 block tables.
+
+Drop-in for the reference's ``core/cache_manager.py`` (``KVCacheManager`` :262-691,
+``store_kvcache`` :143-194, ``store_kvcache_batch`` :196-255): same constructor,
+same methods and return conventions, same observable allocator state
+(``_free`` FIFO deque, ``_blocks``, ``_pos``) — including the reference's quirks,
+which the engine relies on:
+
+  * ``append`` hands out offsets 0..254 of a block and then moves to a NEW block
+    (offset 255 is never returned, cache_manager.py:425);
+  * ``alloc`` with ``n_tokens % block_size == 0`` records the last block as EMPTY
+    (``_pos == 0``, cache_manager.py:384-387);
+  * ``free`` returns blocks to the right end of the FIFO in list order.
+
+What is different is where the data lives: block tables and sequence lengths are
+staged in pinned host mirrors and reach the device with ONE async copy each per
+step (the reference issues one slice-assign kernel per batch row,
+cache_manager.py:530-540); slot maps are built vectorised; the scatter kernel is
+the sm_100a ``b200_store_kvcache`` instead of Triton.  There is no CPU scatter
+path: ``put``/``store_kvcache`` require CUDA tensors.
+"""
+from __future__ import annotations
+
+import collections
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+__all__ = ["KVCacheManager", "store_kvcache", "store_kvcache_batch"]
+
+
+def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                  slot_mapping: torch.Tensor, block_size: int) -> None:
+    """Scatter ``key/value[t]`` to ``cache[slot // block_size, slot % block_size]``; slot -1 skips
+    the token (reference cache_manager.py:143-194).  CUDA only."""
+    num_tokens, num_heads, head_size = key.shape
+    assert key.dim() == 3 and value.dim() == 3
+    assert value.shape == (num_tokens, num_heads, head_size)
+    assert slot_mapping.numel() == num_tokens
+    assert key.is_cuda, "store_kvcache: CUDA tensors required (no CPU path)"
+    from b200ops import store_kvcache as _store
+    slots = slot_mapping.reshape(-1)
+    if slots.dtype != torch.int32:
+        slots = slots.to(torch.int32)
+    _store(key, value, k_cache, v_cache, slots.contiguous(), block_size)
+
+
+def store_kvcache_batch(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                        slot_mapping_batch: torch.Tensor, block_size: int) -> None:
+    """Decode-step variant: ``key/value [B, 1, H, D]``, ``slot_mapping_batch [B, 1]``
+    (reference cache_manager.py:196-255)."""
+    batch_size, num_tokens, num_heads, head_size = key.shape
+    assert key.dim() == 4 and value.dim() == 4
+    assert value.shape == (batch_size, num_tokens, num_heads, head_size)
+    assert slot_mapping_batch.shape == (batch_size, num_tokens)
+    assert num_tokens == 1, "Only support num_tokens=1 for decoding stage"
+    store_kvcache(key.view(-1, num_heads, head_size), value.view(-1, num_heads, head_size),
+                  k_cache, v_cache, slot_mapping_batch.reshape(-1), block_size)
+
+
+class KVCacheManager:
+    def __init__(self, n_blocks: int, block_size: int, n_layers: int, n_heads: int, head_size: int,
+                 dtype=torch.float16, device="cuda", max_tokens: int = 1024, max_batch_size: int = 32):
+        self.n_blocks, self.block_size, self.n_layers = n_blocks, block_size, n_layers
+        self.n_heads, self.head_size = n_heads, head_size
+        self.dtype, self.device = dtype, device
+
+        # one zero-filled slab, exposed per layer with the reference's shapes
+        # [n_blocks, block_size, n_heads, head_size] (cache_manager.py:311-323)
+        self._storage = torch.zeros((n_layers, 2, n_blocks, block_size, n_heads, head_size),
+                                    dtype=dtype, device=device)
+        self.k_caches = [self._storage[i, 0] for i in range(n_layers)]
+        self.v_caches = [self._storage[i, 1] for i in range(n_layers)]
+
+        self._free = collections.deque(range(n_blocks))      # FIFO of free block ids
+        self._blocks = {}                                     # seq_id -> [block ids]
+        self._pos = {}                                        # block id -> used slots
+
+        self.cache_seqlens = torch.tensor([1], dtype=torch.int32, device=device)
+        self.max_tokens = max_tokens
+        self.max_seq_blocks = (max_tokens + block_size - 1) // block_size
+        self.max_batch_size = max_batch_size
+        self._block_table_buffer = torch.full((max_batch_size, self.max_seq_blocks), -1,
+                                              dtype=torch.int32, device=device)
+        self._cache_seqlens_buffer = torch.zeros(max_batch_size, dtype=torch.int32, device=device)
+
+        # Pinned host mirrors: filled with numpy, shipped with one async copy each per step.
+        # Two sets alternate and each carries the event of the copy that last read it, so the
+        # host can run one step ahead of the device without overwriting bytes still in flight.
+        self._on_gpu = torch.cuda.is_available() and torch.device(device).type == "cuda"
+        self._stages = []
+        for _ in range(2):
+            bt = torch.full((max_batch_size, self.max_seq_blocks), -1, dtype=torch.int32, pin_memory=self._on_gpu)
+            sl = torch.zeros(max_batch_size, dtype=torch.int32, pin_memory=self._on_gpu)
+            self._stages.append({"bt": bt, "sl": sl, "bt_np": bt.numpy(), "sl_np": sl.numpy(), "event": None})
+        self._stage_idx = 0
+
+    # ------------------------------------------------------------------ allocator
+    def alloc(self, seq_id: int, n_tokens: int) -> Tuple[bool, Optional[torch.Tensor]]:
+        bs = self.block_size
+        need = -(-n_tokens // bs)
+        if len(self._free) < need:
+            return False, None
+        blocks = [self._free.popleft() for _ in range(need)]
+        for b in blocks:
+            self._pos[b] = bs
+        if blocks:
+            self._pos[blocks[-1]] = n_tokens % bs            # 0 when n_tokens is a multiple of bs (reference quirk)
+        self._blocks[seq_id] = blocks
+        idx = np.arange(n_tokens, dtype=np.int64)
+        if n_tokens:
+            slots = np.asarray(blocks, dtype=np.int64)[idx // bs] * bs + idx % bs
+        else:
+            slots = idx
+        slot_mapping = torch.from_numpy(slots.astype(np.int32))
+        if torch.device(self.device).type != "cpu":
+            slot_mapping = slot_mapping.to(self.device)
+        return True, slot_mapping
+
+    def append(self, seq_id: int) -> int:
+        blocks = self._blocks.get(seq_id)
+        if blocks is None:
+            return -1
+        last = blocks[-1]
+        used = self._pos[last]
+        if used < self.block_size - 1:                        # offsets 0..254 only (reference quirk)
+            self._pos[last] = used + 1
+            return last * self.block_size + used
+        if self._free:
+            new = self._free.popleft()
+            blocks.append(new)
+            self._pos[new] = 1
+            return new * self.block_size
+        print(f"cache_manager.append failed for seq {seq_id}: blocks={blocks} pos={used} "
+              f"block_size={self.block_size} free={len(self._free)}")
+        return -1
+
+    def free(self, seq_id: int) -> None:
+        blocks = self._blocks.pop(seq_id, None)
+        if blocks is None:
+            return
+        for b in blocks:
+            self._free.append(b)
+            self._pos.pop(b, None)
+
+    def reset(self) -> None:
+        self._free = collections.deque(range(self.n_blocks))
+        self._blocks.clear()
+        self._pos.clear()
+
+    # ------------------------------------------------------------------ cache access
+    def put(self, seq_id: int, key: torch.Tensor, value: torch.Tensor, layer: int, slot_map: torch.Tensor) -> None:
+        store_kvcache(key, value, self.k_caches[layer], self.v_caches[layer], slot_map, self.block_size)
+
+    def get(self, layer: int, block_id: int = None):
+        k, v = self.k_caches[layer], self.v_caches[layer]
+        return (k[block_id], v[block_id]) if block_id is not None else (k, v)
+
+    def get_blocks(self, seq_id: int) -> List[int]:
+        return self._blocks.get(seq_id, [])                  # live reference, as in the reference (:506)
+
+    def get_slots(self, seq_id: int, token_positions: list) -> list:
+        blocks = self._blocks.get(seq_id)
+        if blocks is None:
+            return [-1] * len(token_positions)
+        bs = self.block_size
+        out = []
+        for pos in token_positions:
+            bi, off = divmod(pos, bs)
+            if bi >= len(blocks) or off >= self._pos.get(blocks[bi], 0):
+                out.append(-1)
+            else:
+                out.append(blocks[bi] * bs + off)
+        return out
+
+    # ------------------------------------------------------------------ per-step device metadata
+    def cache_batch_data(self, seq_ids: list, context_lens: list):
+        """Refresh rows ``[:B]`` of the static device buffers (block ids, -1 padded) and
+        ``cache_seqlens[:B]``; returns views of the same device memory every time
+        (reference cache_manager.py:509-546)."""
+        B = len(seq_ids)
+        if B > 0:
+            stage = self._stages[self._stage_idx]
+            self._stage_idx ^= 1
+            if stage["event"] is not None:
+                stage["event"].synchronize()
+            bt = stage["bt_np"]
+            bt[:B] = -1
+            for i, sid in enumerate(seq_ids):
+                blocks = self._blocks.get(sid)
+                if blocks:
+                    bt[i, :len(blocks)] = blocks               # raises if a sequence outgrew max_tokens, like the reference
+            stage["sl_np"][:B] = context_lens
+            self._block_table_buffer[:B].copy_(stage["bt"][:B], non_blocking=True)
+            self._cache_seqlens_buffer[:B].copy_(stage["sl"][:B], non_blocking=True)
+            if self._on_gpu:
+                if stage["event"] is None:
+                    stage["event"] = torch.cuda.Event()
+                stage["event"].record()
+        return self._block_table_buffer[:B], self._cache_seqlens_buffer[:B]
+
+    def get_buffer_data(self, seq_ids: list):
+        B = len(seq_ids)
+        return self._block_table_buffer[:B], self._cache_seqlens_buffer[:B]
+
+    # ------------------------------------------------------------------ monitoring
+    @property
+    def stats(self) -> dict:
+        total, free = self.n_blocks, len(self._free)
+        longest = run = 0
+        prev = None
+        for b in sorted(self._free):
+            run = run + 1 if prev is not None and b == prev + 1 else 1
+            longest = max(longest, run)
+            prev = b
+        frag = 1.0 - longest / max(free, 1) if free > 0 else 0.0
+        return {"total": total, "free": free, "used": total - free, "frag": round(frag, 3)}

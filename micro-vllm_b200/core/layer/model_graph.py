@@ -1,0 +1,185 @@
+"""Decode runner: static buffers, per-layer op sequence, CUDA-graph capture per batch size.
+
+Drop-in for the reference's ``core/layer/model_graph.py`` (``ModelGraphRunner`` :25-260) with
+the same constructor, ``prepare_weights`` / ``capture`` / ``forward`` / ``decode`` surface and
+the same Qwen-1-style module tree (``transformer.h[i].attn.c_attn`` ...).  Differences, all on
+the hot path this repo owns:
+
+  * attention is ``b200ops.paged_attn_decode`` (fused RoPE + KV append + split-KV + merge,
+    one launch) writing a STATIC output buffer, instead of ``flash_attn_with_kvcache``
+    (:161-168) which allocates its output inside the captured region;
+  * q/k/v are split GQA-aware (``Hq`` + 2 x ``Hkv`` heads); the reference's
+    ``reshape(bs, 3, H, D)`` (:152) only works for MHA;
+  * the MLP always runs matmul -> ``swiglu_gemm`` -> matmul (the reference's
+    ``fast_mode=False`` branch, :183-186); the Inductor-compiled ``_mlp`` (:51, :199) is gone —
+    no torch.compile on the path;
+  * an un-captured batch size runs eagerly against the REAL block table (the reference
+    substitutes an all-zero table there, :158/:257-258, which is only right during warm-up).
+
+GEMMs stay ``torch.matmul(..., out=)`` (cuBLAS; out of scope) and the two
+all-reduces per layer stay NCCL (``core.parallel_config.all_reduce``).
+"""
+import logging
+from typing import Dict, List
+
+import torch
+
+import b200ops
+from core.paged_attention import PagedAttention
+from core.parallel_config import all_reduce, get_rank, get_world_size
+from kernel.rmsnorm_add import rmsnorm_
+from kernel.rmsnorm_residual import rmsnorm_residual_gemm
+from kernel.swiglu import swiglu_gemm
+from .rope import RoPE
+
+logger = logging.getLogger(__name__)
+
+
+class ModelGraphRunner:
+    def __init__(self, model, num_layers: int, num_heads: int, head_size: int,
+                 kv_num_heads: int, hidden_dim: int, intermediate_size: int,
+                 device: str, max_batch_size: int = 32, dtype: torch.dtype = torch.bfloat16,
+                 top_k: int = 1000, max_blocks: int = 32):
+        """``num_heads`` / ``kv_num_heads`` are the LOCAL (per-rank) head counts and
+        ``intermediate_size`` is the local width of the packed gate|up activation divided the
+        way the engine does it (engine.py:108-114): i.e. this rank's ``2 * I / world_size``
+        when the caller follows the reference and passes ``config.intermediate_size // ws``
+        of a Qwen-1 config, whose ``intermediate_size`` already counts gate + up."""
+        self.model = model
+        self.num_layers = num_layers
+        self.rank, self.world_size = get_rank(), get_world_size()
+        self.num_heads = num_heads
+        self.kv_num_heads = kv_num_heads
+        self.intermediate_size = intermediate_size
+        self.head_size = head_size
+        self.hidden_dim = hidden_dim
+        self.vocab_size = model.config.vocab_size
+        self.device = device
+        self.max_bs = max_batch_size
+        self.dtype = dtype
+        self.top_k = top_k
+
+        self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
+                                        max_blocks=max_blocks, rotary_interleaved=False)
+        self.rope = RoPE()
+        self.prepare_weights()
+        self._alloc_bufs()
+        self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
+        self._is_graph_ready = False
+
+    # ------------------------------------------------------------------ init
+    @staticmethod
+    def _mlp(x, gu_weight, d_weight):
+        """Eager statement of the MLP (reference :75-81): columns [0, d) of gate_up are ``up``."""
+        gate_up = x @ gu_weight
+        up, gate = gate_up.chunk(2, dim=-1)
+        return (torch.nn.functional.silu(gate) * up) @ d_weight
+
+    def prepare_weights(self):
+        """Per-rank slices, transposed to [in, out] contiguous (reference :87-118)."""
+        cfg = self.model.config
+        g_heads = cfg.num_attention_heads
+        g_kv = getattr(cfg, "num_key_value_heads", g_heads)
+        q_dim, kv_dim = g_heads * self.head_size, g_kv * self.head_size
+        ws, r = self.world_size, self.rank
+        for block in self.model.transformer.h:
+            w1, w2 = block.mlp.w1.weight, block.mlp.w2.weight
+            block.mlp._gu = torch.cat([w1.chunk(ws, dim=0)[r], w2.chunk(ws, dim=0)[r]], dim=0).t().contiguous()
+            block.mlp._d = block.mlp.c_proj.weight.chunk(ws, dim=1)[r].t().contiguous()
+            block.attn._o = block.attn.c_proj.weight.chunk(ws, dim=1)[r].t().contiguous()
+            w_q, w_k, w_v = block.attn.c_attn.weight.split([q_dim, kv_dim, kv_dim], dim=0)
+            block.attn._qkv_w = torch.cat([w.chunk(ws, dim=0)[r] for w in (w_q, w_k, w_v)], dim=0).t().contiguous()
+            bias = block.attn.c_attn.bias
+            block.attn._qkv_b = None
+            if bias is not None:
+                b_q, b_k, b_v = bias.split([q_dim, kv_dim, kv_dim], dim=0)
+                block.attn._qkv_b = torch.cat([b.chunk(ws, dim=0)[r] for b in (b_q, b_k, b_v)], dim=0)
+
+    def _alloc_bufs(self):
+        mb, dev, dt = self.max_bs, self.device, self.dtype
+        blk = self.model.transformer.h[0]
+        qkv_dim, o_in = blk.attn._qkv_w.shape[1], blk.attn._o.shape[0]
+        gu_dim = blk.mlp._gu.shape[1]
+        self._input_ids = torch.empty(mb, dtype=torch.long, device=dev)
+        self._logits = torch.empty(mb, self.vocab_size, dtype=dt, device=dev)
+        self._normed = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        self._qkv = torch.empty((mb, qkv_dim), dtype=dt, device=dev)
+        self._attn = torch.empty((mb, o_in), dtype=dt, device=dev)
+        self._attn_out = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        self._residual = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        self._gate_up = torch.empty((mb, gu_dim), dtype=dt, device=dev)
+        self._swiglu_out = torch.empty((mb, gu_dim // 2), dtype=dt, device=dev)
+        self._mlp_out = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
+
+    # ------------------------------------------------------------------ per-layer pieces
+    def _qkv_proj(self, h, block, bs):
+        rmsnorm_(h, block.ln_1.weight, self._normed[:bs], block.ln_1.eps)
+        qkv = self._qkv[:bs]
+        torch.matmul(self._normed[:bs], block.attn._qkv_w, out=qkv)
+        if block.attn._qkv_b is not None:
+            qkv.add_(block.attn._qkv_b)
+        return qkv
+
+    def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache):
+        Hq, Hkv, D = self.num_heads, self.kv_num_heads, self.head_size
+        q = qkv[:, : Hq * D].view(bs, Hq, D)
+        k = qkv[:, Hq * D: (Hq + Hkv) * D].view(bs, Hkv, D)
+        v = qkv[:, (Hq + Hkv) * D:].view(bs, Hkv, D)
+        k_cache, v_cache = cache_manager.get(layer_idx)
+        cache_lens = cache_manager._cache_seqlens_buffer[:bs]
+        # warm-up before capture runs against an all-zero table, like the reference (:158)
+        block_table = cache_manager._block_table_buffer[:bs] if use_graph_cache else self._zero_table[:bs]
+        attn = self._attn[:bs].view(bs, Hq, D)
+        b200ops.paged_attn_decode(q, k_cache, v_cache, k, v,
+                                  self.attention._cos_pool, self.attention._sin_pool,
+                                  cache_lens, block_table, softmax_scale=self.attention.scale,
+                                  rotary_interleaved=False, out=attn)
+        out = self._attn_out[:bs]
+        torch.matmul(self._attn[:bs], block.attn._o, out=out)
+        return out
+
+    def _ffn(self, x_normed, block, bs, fast_mode=False):
+        torch.matmul(x_normed, block.mlp._gu, out=self._gate_up[:bs])
+        swiglu_gemm(self._gate_up[:bs], self._swiglu_out[:bs])
+        torch.matmul(self._swiglu_out[:bs], block.mlp._d, out=self._mlp_out[:bs])
+        return self._mlp_out[:bs]
+
+    # ------------------------------------------------------------------ decode step
+    def decode(self, input_ids, bs, cache_manager, use_graph_cache):
+        h = self.model.transformer.wte(input_ids)
+        for layer_idx in range(self.num_layers):
+            block = self.model.transformer.h[layer_idx]
+            qkv = self._qkv_proj(h, block, bs)
+            attn_out = all_reduce(self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache))
+            rmsnorm_residual_gemm(attn_out, h, block.ln_2.weight, self._normed[:bs], self._residual[:bs],
+                                  block.ln_2.eps)
+            mlp_out = self._ffn(self._normed[:bs], block, bs)
+            h = all_reduce(mlp_out).add_(self._residual[:bs])
+        return self.model.lm_head(self.model.transformer.ln_f(h))
+
+    def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32]):
+        """3 eager warm-ups then ``torch.cuda.graph`` per batch size (reference :225-253)."""
+        if self._is_graph_ready:
+            return
+        for bs in batch_sizes:
+            dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
+            with torch.no_grad():
+                for _ in range(3):
+                    self.decode(dummy, bs, cache_manager, use_graph_cache=False)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.no_grad(), torch.cuda.graph(g):
+                self._logits[:bs] = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True)
+            self._graphs[bs] = g
+            logger.info("captured decode graph for batch size %d", bs)
+        self._is_graph_ready = True
+
+    def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
+        self._input_ids[:batch_size] = input_ids
+        g = self._graphs.get(batch_size)
+        if g is None:
+            with torch.no_grad():
+                return self.decode(input_ids, batch_size, cache_manager, use_graph_cache=True)
+        g.replay()
+        return self._logits[:batch_size]

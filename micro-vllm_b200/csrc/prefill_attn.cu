@@ -1,0 +1,552 @@
+// Paged prefill attention for sm_100a on tcgen05 tensor cores — replaces
+// RoPE.forward (core/layer/rope.py:10-39) + flash_attn_with_kvcache at
+// core/layer/model_prefill.py:49-52.
+//
+// Two launches per layer call:
+//   1. prefill_rope_append_kernel: rotate q and k at positions P_b + i (fp32, one
+//      rounding), scatter rotated K and raw V into the pages named by block_table,
+//      stage rotated Q in a workspace.                       (HBM-bound, elementwise)
+//   2. prefill_attn_kernel: one CTA = 128 query rows of one head.  A TMA producer
+//      warp streams Q and 128-token K/V tiles straight out of the paged cache
+//      (4-D tensor map: d, head, slot, page -> the page id is a TMA coordinate,
+//      128B-swizzled so the tiles are UMMA-canonical).  One thread issues
+//      tcgen05.mma: S = Q.K^T into a double-buffered TMEM accumulator and
+//      O += P.V into a second TMEM accumulator (V is consumed MN-major, no
+//      transpose).  Four softmax warps own one query row per thread (TMEM lane =
+//      row): tcgen05.ld the scores, online softmax in fp32 with lazy rescaling,
+//      write P as a K-major bf16 operand to shared memory, rescale O in TMEM only
+//      when the running max moved by more than 2^8.            (tensor-core bound)
+#include "common.cuh"
+#include <cuda.h>
+#include <math_constants.h>
+
+namespace b200 {
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Bounded spin: a protocol bug traps (launch error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+                 " [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(map) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], bf16 x bf16 -> fp32, issued by ONE thread
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+                 "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+                 "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 :: "r"(taddr),
+                    "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                    "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+                    "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+                    "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory matrix descriptor, SWIZZLE_128B, Blackwell version bit set
+// (bit layout: cute/arch/mma_sm100_desc.hpp UMMA::SmemDescriptor).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu)
+         | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16)
+         | ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32)
+         | (1ull << 46)            // descriptor version (sm_100)
+         | (2ull << 61);           // LayoutType::SWIZZLE_128B
+}
+// Instruction descriptor for kind::f16, bf16 inputs, fp32 accumulate (UMMA::InstrDescriptor).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16)
+         | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------ kernel 1: RoPE + append
+struct AppendParams {
+    const __nv_bfloat16* q; const __nv_bfloat16* k; const __nv_bfloat16* v;
+    __nv_bfloat16* k_cache; __nv_bfloat16* v_cache; __nv_bfloat16* q_rot;
+    const __nv_bfloat16* cos; const __nv_bfloat16* sin;
+    const int32_t* seqlens; const int32_t* block_table;
+    int B, S, Hq, Hkv, D, rotary_dim, interleaved, rot_rows;
+    int n_blocks, block_size, max_blocks_per_seq;
+    int64_t q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh;
+    int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
+};
+
+__global__ void __launch_bounds__(128)
+prefill_rope_append_kernel(const __grid_constant__ AppendParams p) {
+    const int s = blockIdx.x, b = blockIdx.y;
+    const int D = p.D, JB = D / 16, CPR = D / 8;
+    const int pos = __ldg(p.seqlens + b) + s;
+    const int rd = p.cos ? p.rotary_dim : 0;
+    const int rpos = min(pos, p.rot_rows - 1);
+    const __nv_bfloat16* cosr = p.cos ? p.cos + (int64_t)rpos * (p.rotary_dim >> 1) : nullptr;
+    const __nv_bfloat16* sinr = p.sin ? p.sin + (int64_t)rpos * (p.rotary_dim >> 1) : nullptr;
+    const int pe = pos / p.block_size;
+    const int page = (pe < p.max_blocks_per_seq) ? __ldg(p.block_table + (int64_t)b * p.bt_sb + pe) : -1;
+    const bool page_ok = page >= 0 && page < p.n_blocks;
+    const int slot = pos - pe * p.block_size;
+
+    const int q_tasks = p.Hq * JB, k_tasks = p.Hkv * JB, v_tasks = p.Hkv * CPR;
+    for (int t = threadIdx.x; t < q_tasks + k_tasks + v_tasks; t += blockDim.x) {
+        if (t < q_tasks) {
+            const int h = t / JB, j = t - h * JB;
+            const __nv_bfloat16* src = p.q + (int64_t)b * p.q_sb + (int64_t)s * p.q_ss + (int64_t)h * p.q_sh;
+            __nv_bfloat16* dst = p.q_rot + (((int64_t)b * p.S + s) * p.Hq + h) * D;
+            rope_block(src, j, rd, p.interleaved != 0, cosr, sinr,
+                       [&](int c, const uint4& v) { *reinterpret_cast<uint4*>(dst + c * 8) = v; });
+        } else if (t < q_tasks + k_tasks) {
+            if (!page_ok) continue;
+            const int u = t - q_tasks;
+            const int h = u / JB, j = u - h * JB;
+            const __nv_bfloat16* src = p.k + (int64_t)b * p.k_sb + (int64_t)s * p.k_ss + (int64_t)h * p.k_sh;
+            __nv_bfloat16* dst = p.k_cache + (int64_t)page * p.kc_sblk + (int64_t)slot * p.kc_stok + (int64_t)h * p.kc_sh;
+            rope_block(src, j, rd, p.interleaved != 0, cosr, sinr,
+                       [&](int c, const uint4& v) { *reinterpret_cast<uint4*>(dst + c * 8) = v; });
+        } else {
+            if (!page_ok) continue;
+            const int u = t - q_tasks - k_tasks;
+            const int h = u / CPR, c = u - h * CPR;
+            const __nv_bfloat16* src = p.v + (int64_t)b * p.v_sb + (int64_t)s * p.v_ss + (int64_t)h * p.v_sh;
+            __nv_bfloat16* dst = p.v_cache + (int64_t)page * p.vc_sblk + (int64_t)slot * p.vc_stok + (int64_t)h * p.vc_sh;
+            *reinterpret_cast<uint4*>(dst + c * 8) = ld_v4(src + c * 8);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ kernel 2: attention
+struct PrefillParams {
+    const int32_t* seqlens; const int32_t* block_table; __nv_bfloat16* out;
+    int B, S, Hq, Hkv, G;
+    int n_blocks, block_size, max_blocks_per_seq, causal;
+    int64_t o_sb, o_ss, o_sh, bt_sb;
+    float scale_log2;
+};
+
+template <int D_>
+struct PCfg {
+    static constexpr int D = D_;
+    static constexpr int BM = 128, BN = 128;
+    static constexpr int SLAB_B = 128 * 128;                  // 128 rows x 128 B (64 bf16), one TMA box
+    static constexpr int DSLABS = D / 64;                     // slabs along head_dim
+    static constexpr int TILE_B = DSLABS * SLAB_B;            // Q, K or V tile
+    static constexpr int P_B = 2 * SLAB_B;                    // P [128 x 128 tokens] = 2 K-major slabs
+    static constexpr int KV_STAGES = 2;
+    static constexpr int OFF_Q = 0;
+    static constexpr int OFF_K = OFF_Q + TILE_B;
+    static constexpr int OFF_V = OFF_K + KV_STAGES * TILE_B;
+    static constexpr int OFF_P = OFF_V + KV_STAGES * TILE_B;
+    static constexpr int OFF_BAR = OFF_P + P_B;
+    static constexpr int NBARS = 16;
+    static constexpr int SMEM = OFF_BAR + NBARS * 8 + 16 + 1024;   // +1024: manual 1 KB alignment
+    static constexpr int THREADS = 192;                       // warp0 TMA, warp1 MMA, warps2-5 softmax
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int TM_S0 = 0, TM_S1 = 128, TM_O = 256;
+};
+
+enum { BAR_Q = 0, BAR_KF = 1, BAR_KE = 3, BAR_VF = 5, BAR_VE = 7, BAR_SF = 9, BAR_SE = 11, BAR_PF = 13, BAR_PE = 14 };
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                    const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ PrefillParams p) {
+    constexpr int D = C::D;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_u32 = smem_u32(smem_raw);
+    const uint32_t base = (raw_u32 + 1023u) & ~1023u;          // SWIZZLE_128B atoms need 1 KB alignment
+    uint8_t* smem = smem_raw + (base - raw_u32);
+    const uint32_t sQ = base + C::OFF_Q, sK = base + C::OFF_K, sV = base + C::OFF_V, sP = base + C::OFF_P;
+    const uint32_t bars = base + C::OFF_BAR;
+    auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
+    volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qt = (int)gridDim.x - 1 - (int)blockIdx.x;       // heaviest (last) causal tiles first
+    const int q0 = qt * C::BM;
+    const int hq = blockIdx.y, b = blockIdx.z;
+    const int kvh = hq / p.G;
+    const int prefix = __ldg(p.seqlens + b);
+    const int seqlen_k = prefix + p.S;
+    const int kv_end = p.causal ? min(seqlen_k, prefix + q0 + C::BM) : seqlen_k;
+    const int n_tiles = (kv_end + C::BN - 1) / C::BN;
+
+    if (tid == 0) {
+        mbar_init(bar(BAR_Q), 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bar(BAR_KF + s), 1); mbar_init(bar(BAR_KE + s), 1);
+            mbar_init(bar(BAR_VF + s), 1); mbar_init(bar(BAR_VE + s), 1);
+            mbar_init(bar(BAR_SF + s), 1); mbar_init(bar(BAR_SE + s), 128);
+        }
+        mbar_init(bar(BAR_PF), 128); mbar_init(bar(BAR_PE), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32((const void*)s_tmem)), "r"((uint32_t)C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer
+        if (lane == 0) {
+            mbar_expect_tx(bar(BAR_Q), C::TILE_B);
+#pragma unroll
+            for (int sl = 0; sl < C::DSLABS; ++sl)
+                tma_load_4d(sQ + sl * C::SLAB_B, &tm_q, bar(BAR_Q), sl * 64, hq, q0, b);
+            const int32_t* bt = p.block_table + (int64_t)b * p.bt_sb;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                const int n0 = j * C::BN;
+                const int pe = n0 / p.block_size;
+                int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : 0;
+                if (page < 0 || page >= p.n_blocks) page = 0;          // memory safety; tokens are masked or undefined
+                const int tok = n0 - pe * p.block_size;
+                mbar_wait(bar(BAR_KE + st), ph ^ 1u);
+                mbar_expect_tx(bar(BAR_KF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(BAR_KF + st), sl * 64, kvh, tok, page);
+                mbar_wait(bar(BAR_VE + st), ph ^ 1u);
+                mbar_expect_tx(bar(BAR_VF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sV + st * C::TILE_B + sl * C::SLAB_B, &tm_v, bar(BAR_VF + st), sl * 64, kvh, tok, page);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer (one thread)
+        if (lane == 0) {
+            constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q K-major, B=K K-major
+            constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P K-major, B=V MN-major
+            auto issue_pv = [&](int t) {
+                const int st = t & 1;
+                mbar_wait(bar(BAR_VF + st), (uint32_t)(t >> 1) & 1u);
+                mbar_wait(bar(BAR_PF), (uint32_t)t & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < C::BN / 16; ++k) {
+                    // A: P[128 x 16 tokens], K-major slab k/4, +32 B per k-step inside the 128 B swizzle row
+                    const uint64_t da = umma_desc_sw128(sP + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    // B: V[16 tokens x D], MN-major: 16 token rows = 2 KB per k-step, d-slabs 16 KB apart
+                    const uint64_t db = umma_desc_sw128(sV + st * C::TILE_B + k * 2048, C::SLAB_B, 1024);
+                    umma_bf16(tmem + C::TM_O, da, db, IDESC_PV, (t > 0 || k > 0) ? 1u : 0u);
+                }
+                tc_commit(bar(BAR_VE + st));       // V stage free once these MMAs retire
+                tc_commit(bar(BAR_PE));            // P buffer free, O updated
+            };
+            mbar_wait(bar(BAR_Q), 0);
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                mbar_wait(bar(BAR_KF + st), ph);
+                mbar_wait(bar(BAR_SE + st), ph ^ 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t da = umma_desc_sw128(sQ + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    const uint64_t db = umma_desc_sw128(sK + st * C::TILE_B + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    umma_bf16(tmem + (st ? C::TM_S1 : C::TM_S0), da, db, IDESC_QK, k > 0 ? 1u : 0u);
+                }
+                tc_commit(bar(BAR_KE + st));
+                tc_commit(bar(BAR_SF + st));
+                if (j > 0) issue_pv(j - 1);        // QK_j is queued ahead of PV_{j-1}: tensor pipe works while softmax j-1 runs
+            }
+            issue_pv(n_tiles - 1);
+        }
+    } else {
+        // ===================================================== softmax / correction / epilogue (4 warps, 1 row per thread)
+        const int quarter = warp & 3;                          // TMEM lane quarter this warp may access
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
+        const float sl2 = p.scale_log2;
+        float m_ref = -CUDART_INF_F, l = 0.0f;
+        const uint32_t p_row = sP + (uint32_t)row * 128u;
+        const int sw = row & 7;
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int st = j & 1;
+            const int n0 = j * C::BN;
+            mbar_wait(bar(BAR_SF + st), (uint32_t)(j >> 1) & 1u);
+            tc_fence_after();
+            uint32_t su[C::BN];                                // scores, fp32 bit patterns (TMEM registers)
+#define SF(c) __uint_as_float(su[(c)])
+            {
+                const uint32_t ts = tmem + lane_sel + (st ? C::TM_S1 : C::TM_S0);
+#pragma unroll
+                for (int c = 0; c < C::BN / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(ts + c * 32, r);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) su[c * 32 + i] = r[i];
+                }
+                tmem_wait_ld();
+            }
+            tc_fence_before();
+            mbar_arrive(bar(BAR_SE + st));                     // S buffer may be overwritten by QK_{j+2}
+
+            if (n0 + C::BN - 1 > prefix + q0 || n0 + C::BN > seqlen_k) {   // diagonal or tail tile
+#pragma unroll
+                for (int c = 0; c < C::BN; ++c) {
+                    const int tok = n0 + c;
+                    if (tok > qpos || tok >= seqlen_k) su[c] = 0xff800000u;   // -inf
+                }
+            }
+            float mx = SF(0);
+#pragma unroll
+            for (int c = 1; c < C::BN; ++c) mx = fmaxf(mx, SF(c));
+            // lazy rescale: keep the old reference max unless it is off by more than 2^8
+            float alpha = 1.0f;
+            bool grow = false;
+            if (j == 0) {
+                m_ref = mx;
+            } else if ((mx - m_ref) * sl2 > 8.0f) {
+                alpha = fast_exp2((m_ref - mx) * sl2);
+                m_ref = mx;
+                l *= alpha;
+                grow = true;
+            }
+            const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
+            float rs = 0.0f;
+#pragma unroll
+            for (int c = 0; c < C::BN; ++c) { const float e = fast_exp2(SF(c) * sl2 - mr); su[c] = __float_as_uint(e); rs += e; }
+            l += rs;
+
+            mbar_wait(bar(BAR_PE), ((uint32_t)j & 1u) ^ 1u);   // PV_{j-1} retired: P buffer free, O stable
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < C::BN / 8; ++c) {              // 16-byte chunks of 8 tokens, K-major SW128
+                uint4 v;
+                v.x = pack_bf16(SF(c * 8 + 0), SF(c * 8 + 1));
+                v.y = pack_bf16(SF(c * 8 + 2), SF(c * 8 + 3));
+                v.z = pack_bf16(SF(c * 8 + 4), SF(c * 8 + 5));
+                v.w = pack_bf16(SF(c * 8 + 6), SF(c * 8 + 7));
+                const uint32_t addr = p_row + (uint32_t)(c >> 3) * C::SLAB_B + (uint32_t)(((c & 7) ^ sw) << 4);
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+            }
+            if (j > 0 && __any_sync(0xffffffffu, grow)) {      // warp-uniform: tcgen05.ld/st are warp-collective
+                const uint32_t to = tmem + lane_sel + C::TM_O;
+#pragma unroll
+                for (int c = 0; c < D / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(to + c * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                    tmem_st32(to + c * 32, r);
+                }
+                tmem_wait_st();
+            }
+            fence_async_smem();                                // P (generic proxy) -> visible to the tensor core (async proxy)
+            tc_fence_before();
+            mbar_arrive(bar(BAR_PF));
+#undef SF
+        }
+
+        // epilogue: O / l -> bf16 -> global
+        mbar_wait(bar(BAR_PE), (uint32_t)(n_tiles - 1) & 1u);
+        tc_fence_after();
+        const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
+        const bool live = (q0 + row) < p.S;
+        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh;
+        const uint32_t to = tmem + lane_sel + C::TM_O;
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(to + c * 32, r);
+            tmem_wait_ld();
+            if (live) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 v;
+                    v.x = pack_bf16(__uint_as_float(r[i * 8 + 0]) * inv, __uint_as_float(r[i * 8 + 1]) * inv);
+                    v.y = pack_bf16(__uint_as_float(r[i * 8 + 2]) * inv, __uint_as_float(r[i * 8 + 3]) * inv);
+                    v.z = pack_bf16(__uint_as_float(r[i * 8 + 4]) * inv, __uint_as_float(r[i * 8 + 5]) * inv);
+                    v.w = pack_bf16(__uint_as_float(r[i * 8 + 6]) * inv, __uint_as_float(r[i * 8 + 7]) * inv);
+                    *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)ptr;
+    }
+    return fn;
+}
+
+// 4-D bf16 map (d, head, row, outer) with a (64, 1, 128, 1) box, 128B swizzle.
+static int make_map(CUtensorMap* map, const void* base, uint64_t d, uint64_t heads, uint64_t rows, uint64_t outer,
+                    uint64_t stride_h, uint64_t stride_row, uint64_t stride_outer /* elements */) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("prefill: cuTensorMapEncodeTiled entry point not available"); return B200_E_UNSUPPORTED; }
+    cuuint64_t dims[4] = {d, heads, rows, outer};
+    cuuint64_t strides[3] = {stride_h * 2, stride_row * 2, stride_outer * 2};
+    cuuint32_t box[4] = {64, 1, 128, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("prefill: cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return B200_E_UNSUPPORTED; }
+    return 0;
+}
+
+template <class C>
+static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                          const PrefillParams& p, cudaStream_t st) {
+    static int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
+        attr_dev = dev;
+    }
+    dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
+    prefill_attn_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tq, tk, tv, p);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D) {
+    if (B <= 0 || S <= 0 || Hq <= 0 || D <= 0) return -1;
+    return (int64_t)B * S * Hq * D * 2;          // rotated Q, bf16
+}
+
+extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream) {
+    if (!a) B200_FAIL(B200_E_NULL, "prefill: null args");
+    if (!a->q || !a->k || !a->v || !a->k_cache || !a->v_cache || !a->cache_seqlens || !a->block_table || !a->out)
+        B200_FAIL(B200_E_NULL, "prefill: required pointer is null");
+    if ((a->rotary_cos == nullptr) != (a->rotary_sin == nullptr)) B200_FAIL(B200_E_NULL, "prefill: rotary_cos and rotary_sin must be given together");
+    if (a->B <= 0 || a->S <= 0 || a->Hq <= 0 || a->Hkv <= 0) B200_FAIL(B200_E_RANGE, "prefill: B=%d S=%d Hq=%d Hkv=%d", a->B, a->S, a->Hq, a->Hkv);
+    if (a->Hq % a->Hkv != 0) B200_FAIL(B200_E_SHAPE, "prefill: Hq=%d not divisible by Hkv=%d", a->Hq, a->Hkv);
+    if (a->D != 64 && a->D != 128) B200_FAIL(B200_E_SHAPE, "prefill: head_dim %d unsupported (64, 128)", a->D);
+    if (a->block_size <= 0 || a->block_size % 128 != 0) B200_FAIL(B200_E_SHAPE, "prefill: block_size %d must be a multiple of 128", a->block_size);
+    if (a->n_blocks <= 0 || a->max_blocks_per_seq <= 0) B200_FAIL(B200_E_RANGE, "prefill: n_blocks / max_blocks_per_seq");
+    if (a->B > 65535 || a->Hq > 65535) B200_FAIL(B200_E_RANGE, "prefill: grid too large");
+    const bool rot = a->rotary_cos != nullptr;
+    if (rot) {
+        if (a->rotary_dim <= 0 || a->rotary_dim > a->D || a->rotary_dim % 16 != 0)
+            B200_FAIL(B200_E_SHAPE, "prefill: rotary_dim %d must be a multiple of 16 and <= head_dim", a->rotary_dim);
+        if (a->rot_rows <= 0) B200_FAIL(B200_E_RANGE, "prefill: rot_rows");
+        if (!aligned16(a->rotary_cos) || !aligned16(a->rotary_sin)) B200_FAIL(B200_E_ALIGN, "prefill: rotary tables must be 16-byte aligned");
+    }
+    const void* ptrs[] = {a->q, a->k, a->v, a->k_cache, a->v_cache, a->out, a->workspace};
+    for (const void* q : ptrs) if (q && !aligned16(q)) B200_FAIL(B200_E_ALIGN, "prefill: tensors must be 16-byte aligned");
+    const int64_t strides[] = {a->q_stride_b, a->q_stride_s, a->q_stride_h, a->k_stride_b, a->k_stride_s, a->k_stride_h,
+                               a->v_stride_b, a->v_stride_s, a->v_stride_h, a->o_stride_b, a->o_stride_s, a->o_stride_h,
+                               a->kc_stride_blk, a->kc_stride_tok, a->kc_stride_h, a->vc_stride_blk, a->vc_stride_tok, a->vc_stride_h};
+    for (int64_t s : strides) if (s % 8 != 0) B200_FAIL(B200_E_ALIGN, "prefill: strides must be multiples of 8 elements");
+    const int64_t need = b200_prefill_workspace_bytes(a->B, a->S, a->Hq, a->D);
+    if (!a->workspace || a->workspace_bytes < need)
+        B200_FAIL(B200_E_RANGE, "prefill: workspace %lld B < required %lld B", (long long)a->workspace_bytes, (long long)need);
+    cudaStream_t st = (cudaStream_t)stream;
+
+    AppendParams ap;
+    ap.q = (const __nv_bfloat16*)a->q; ap.k = (const __nv_bfloat16*)a->k; ap.v = (const __nv_bfloat16*)a->v;
+    ap.k_cache = (__nv_bfloat16*)a->k_cache; ap.v_cache = (__nv_bfloat16*)a->v_cache; ap.q_rot = (__nv_bfloat16*)a->workspace;
+    ap.cos = (const __nv_bfloat16*)a->rotary_cos; ap.sin = (const __nv_bfloat16*)a->rotary_sin;
+    ap.seqlens = a->cache_seqlens; ap.block_table = a->block_table;
+    ap.B = a->B; ap.S = a->S; ap.Hq = a->Hq; ap.Hkv = a->Hkv; ap.D = a->D;
+    ap.rotary_dim = rot ? a->rotary_dim : 0; ap.interleaved = a->rotary_interleaved; ap.rot_rows = rot ? a->rot_rows : 1;
+    ap.n_blocks = a->n_blocks; ap.block_size = a->block_size; ap.max_blocks_per_seq = a->max_blocks_per_seq;
+    ap.q_sb = a->q_stride_b; ap.q_ss = a->q_stride_s; ap.q_sh = a->q_stride_h;
+    ap.k_sb = a->k_stride_b; ap.k_ss = a->k_stride_s; ap.k_sh = a->k_stride_h;
+    ap.v_sb = a->v_stride_b; ap.v_ss = a->v_stride_s; ap.v_sh = a->v_stride_h;
+    ap.kc_sblk = a->kc_stride_blk; ap.kc_stok = a->kc_stride_tok; ap.kc_sh = a->kc_stride_h;
+    ap.vc_sblk = a->vc_stride_blk; ap.vc_stok = a->vc_stride_tok; ap.vc_sh = a->vc_stride_h;
+    ap.bt_sb = a->bt_stride_b;
+    prefill_rope_append_kernel<<<dim3((unsigned)a->S, (unsigned)a->B), 128, 0, st>>>(ap);
+    B200_CHECK_LAUNCH();
+
+    CUtensorMap tq, tk, tv;
+    int rc;
+    if ((rc = make_map(&tq, a->workspace, a->D, a->Hq, a->S, a->B, a->D, (uint64_t)a->Hq * a->D, (uint64_t)a->S * a->Hq * a->D))) return rc;
+    if ((rc = make_map(&tk, a->k_cache, a->D, a->Hkv, a->block_size, a->n_blocks, a->kc_stride_h, a->kc_stride_tok, a->kc_stride_blk))) return rc;
+    if ((rc = make_map(&tv, a->v_cache, a->D, a->Hkv, a->block_size, a->n_blocks, a->vc_stride_h, a->vc_stride_tok, a->vc_stride_blk))) return rc;
+
+    PrefillParams p;
+    p.seqlens = a->cache_seqlens; p.block_table = a->block_table; p.out = (__nv_bfloat16*)a->out;
+    p.B = a->B; p.S = a->S; p.Hq = a->Hq; p.Hkv = a->Hkv; p.G = a->Hq / a->Hkv;
+    p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq; p.causal = a->causal;
+    p.o_sb = a->o_stride_b; p.o_ss = a->o_stride_s; p.o_sh = a->o_stride_h; p.bt_sb = a->bt_stride_b;
+    p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
+    if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
+    return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
+}

@@ -1,0 +1,91 @@
+"""The C-ABI shared library loads on a CPU-only machine, exports every symbol that
+include/b200_abi.h declares, and rejects bad arguments before touching the device."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200_abi.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    from b200ops import _lib
+    names = declared_symbols()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(_lib.lib, n), f"{n} declared in b200_abi.h but not exported by libb200ops.so"
+    assert sorted(_lib.SIGNATURES) == names, "ctypes binding and header disagree"
+    assert _lib.lib.b200_version() == _lib.ABI_VERSION
+
+
+def test_struct_layout_matches_header():
+    """ctypes struct sizes must match the C structs (checked by compiling a tiny C probe)."""
+    import subprocess, tempfile
+    from b200ops import _lib
+    src = '#include <stdio.h>\n#include "b200_abi.h"\nint main(){printf("%zu %zu\\n", sizeof(b200_decode_args), sizeof(b200_prefill_args));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "p.c")
+        open(c, "w").write(src)
+        exe = os.path.join(d, "p")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
+        dec, pre = map(int, subprocess.check_output([exe]).split())
+    assert ctypes.sizeof(_lib.DecodeArgs) == dec
+    assert ctypes.sizeof(_lib.PrefillArgs) == pre
+
+
+def test_argument_errors_without_device():
+    from b200ops import _lib
+    lib = _lib.lib
+    assert lib.b200_swiglu(None, None, 1, 8, 16, 8, None) == _lib.E_NULL
+    assert b"null" in lib.b200_last_error()
+    assert lib.b200_rmsnorm(None, None, None, 1, 8, 8, 8, 1e-6, 0, None) == _lib.E_NULL
+    assert lib.b200_rmsnorm_residual(None, None, None, None, None, 1, 8, 8, 8, 8, 8, 1e-6, 0, None) == _lib.E_NULL
+    assert lib.b200_store_kvcache(None, None, None, None, None, 1, 1, 8, 8, 8, 8, 8, 1, 256, 8, 8, 8, None) == _lib.E_NULL
+    assert lib.b200_paged_attn_decode(None, None) == _lib.E_NULL
+    assert lib.b200_paged_attn_prefill(None, None) == _lib.E_NULL
+    a = _lib.DecodeArgs()
+    for f in ("q", "k_cache", "v_cache", "cache_seqlens", "block_table", "out"):
+        setattr(a, f, 0x1000)
+    a.B, a.Hq, a.Hkv, a.D = 1, 6, 4, 128
+    assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_SHAPE       # Hq % Hkv
+    a.Hq, a.D = 8, 96
+    assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_SHAPE       # head_dim
+    a.D, a.block_size, a.n_blocks, a.max_blocks_per_seq, a.num_splits = 128, 256, 4, 4, 0
+    assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_RANGE       # num_splits
+    assert lib.b200_decode_workspace_bytes(32, 32, 8, 128, 4) > 32 * 32 * 4 * 128 * 4
+    assert lib.b200_decode_workspace_bytes(32, 30, 8, 128, 4) == -1
+    assert lib.b200_prefill_workspace_bytes(2, 128, 32, 128) == 2 * 128 * 32 * 128 * 2
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+    from kernel.swiglu import swiglu_fused, swiglu_gemm
+    from kernel.rmsnorm_add import rmsnorm, rmsnorm_
+    from kernel.rmsnorm_residual import rmsnorm_residual_gemm
+    x = torch.zeros(2, 16, dtype=torch.bfloat16)
+    w = torch.ones(16, dtype=torch.bfloat16)
+    with pytest.raises(AssertionError):
+        swiglu_fused(x)
+    with pytest.raises(AssertionError):
+        swiglu_gemm(x, torch.zeros(2, 8, dtype=torch.bfloat16))
+    with pytest.raises(AssertionError):
+        rmsnorm(x, w)
+    with pytest.raises(AssertionError):
+        rmsnorm_(x, w, torch.zeros_like(x))
+    with pytest.raises(AssertionError):
+        rmsnorm_residual_gemm(x, x, w, torch.zeros_like(x), torch.zeros_like(x))
+
+
+def test_split_heuristic_is_launch_constant():
+    from b200ops import decode_num_splits
+    assert decode_num_splits(32, 8, 16 * 256) == 5
+    assert decode_num_splits(1, 2, 4 * 256) == 16            # capped by what the table can hold
+    assert decode_num_splits(8, 8, 512 * 256) == 19
+    assert decode_num_splits(64, 8, 32 * 256) >= 1
