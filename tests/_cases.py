@@ -1,0 +1,61 @@
+"""Seeded synthetic inputs for the paged-attention parity tests: bf16
+N(0,1) tensors, block ids drawn from a random permutation of the pool so pages are
+non-contiguous, unused block-table entries -1."""
+import math
+
+import torch
+
+from oracle.rotary import rotary_table_oracle
+
+
+def make_paged_case(B, Hq, Hkv, D, lens, S_new=1, page=256, seed=0, extra_blocks=3, table_width=None,
+                    rot_rows=8192, fill="randn", duplicates=None):
+    """Returns a dict of CPU tensors.  ``lens[b]`` = tokens already in the cache (cache_seqlens).
+    The whole pool holds seeded finite N(0,1) values (never zeros, so a kernel that reads past
+    the end of a sequence shows).  ``duplicates = {row: source_row}`` reproduces the scheduler's
+    padding-by-duplication (scheduler.py:88-92): same block-table row, length and q/k/v."""
+    duplicates = duplicates or {}
+    g = torch.Generator().manual_seed(seed)
+    lens = list(lens)
+    for b, src in duplicates.items():
+        lens[b] = lens[src]
+    need = [max(1, -(-(n + S_new) // page)) for n in lens]
+    n_blocks = sum(need[b] for b in range(B) if b not in duplicates) + extra_blocks
+    width = table_width or max(need)
+    it = iter(torch.randperm(n_blocks, generator=g).tolist())
+    table = torch.full((B, width), -1, dtype=torch.int32)
+    for b in range(B):
+        if b not in duplicates:
+            for j in range(need[b]):
+                table[b, j] = next(it)
+    if fill == "randn":
+        k_cache = torch.randn(n_blocks, page, Hkv, D, generator=g).to(torch.bfloat16)
+        v_cache = torch.randn(n_blocks, page, Hkv, D, generator=g).to(torch.bfloat16)
+    else:
+        k_cache = torch.zeros(n_blocks, page, Hkv, D, dtype=torch.bfloat16)
+        v_cache = torch.zeros(n_blocks, page, Hkv, D, dtype=torch.bfloat16)
+    q = torch.randn(B, S_new, Hq, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(B, S_new, Hkv, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, S_new, Hkv, D, generator=g).to(torch.bfloat16)
+    for b, src in duplicates.items():
+        table[b] = table[src]
+        q[b], k[b], v[b] = q[src], k[src], v[src]
+    cos, sin = rotary_table_oracle(D, rot_rows)
+    return dict(q=q, k=k, v=v, k_cache=k_cache, v_cache=v_cache, cos=cos, sin=sin,
+                seqlens=torch.tensor(lens, dtype=torch.int32), table=table, page=page,
+                scale=1.0 / math.sqrt(D))
+
+
+def to_dev(case, dev="cuda"):
+    return {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in case.items()}
+
+
+def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out"):
+    """north_star tolerance: |a - e| <= 2e-3 + 1e-2 * |e| against the fp32 oracle."""
+    a = actual.float().cpu()
+    e = expected_f32.float().cpu()
+    err = (a - e).abs()
+    lim = atol + rtol * e.abs()
+    bad = err > lim
+    assert not bool(bad.any()), (f"{what}: {int(bad.sum())}/{bad.numel()} elements out of tolerance, "
+                                 f"max abs err {float(err.max()):.4e} at {tuple(torch.nonzero(bad)[0].tolist())}")

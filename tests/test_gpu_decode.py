@@ -1,0 +1,311 @@
+"""Paged decode attention (fused RoPE + KV append + split-KV + merge) against the fp32 oracle.
+
+Bar (north_star): V-cache writes bit-exact; rotated K and outputs within
+|a - e| <= 2e-3 + 1e-2 |e| of the fp32 gather+softmax oracle; block-table indexing exact
+(any wrong page shows up as an O(1) error because pages hold independent N(0,1) data)."""
+import pytest
+import torch
+
+import b200ops
+from core.paged_attention import flash_attn_with_kvcache
+import core.paged_attention as pa
+from oracle.elementwise import bf16_ulp_diff
+from oracle.paged_attention import paged_attention_oracle
+from _cases import assert_close, make_paged_case, to_dev
+
+pytestmark = pytest.mark.gpu
+
+
+def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rotary=True):
+    d = to_dev(case)
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(case["q"], kc_ref, vc_ref,
+                                  case["k"] if append else None, case["v"] if append else None,
+                                  case["cos"] if rotary else None, case["sin"] if rotary else None,
+                                  case["seqlens"], case["table"], case["scale"], causal=True, interleaved=interleaved)
+    got = b200ops.paged_attn_decode(
+        d["q"][:, 0], d["k_cache"], d["v_cache"],
+        d["k"][:, 0] if append else None, d["v"][:, 0] if append else None,
+        d["cos"] if rotary else None, d["sin"] if rotary else None,
+        d["seqlens"], d["table"], softmax_scale=case["scale"], rotary_interleaved=interleaved,
+        num_splits=num_splits, variant=variant)
+    torch.cuda.synchronize()
+    return got, want[:, 0], d, kc_ref, vc_ref
+
+
+def check(case, **kw):
+    got, want, d, kc_ref, vc_ref = run_both(case, **kw)
+    assert_close(got, want, what="attention output")
+    assert torch.equal(d["v_cache"].cpu(), vc_ref), "V cache must be bit-exact (appended rows AND untouched rows)"
+    kd = d["k_cache"].cpu()
+    ulp = bf16_ulp_diff(kd, kc_ref)
+    assert int(ulp.max()) <= 1, f"rotated K differs by {int(ulp.max())} bf16 ulp"
+    assert_close(kd, kc_ref.float(), what="rotated K cache")
+    untouched = (kc_ref == case["k_cache"])
+    assert torch.equal(kd[untouched], kc_ref[untouched]), "K rows that were not appended must be untouched"
+    return got
+
+
+LENS_EDGE = [0, 1, 15, 16, 17, 63, 64, 65, 254, 255, 256, 257, 511, 512, 513, 1000]
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (8, 8, 128), (28, 4, 128), (64, 8, 128), (14, 2, 64), (4, 4, 64), (16, 1, 128)])
+@pytest.mark.parametrize("interleaved", [False, True])
+def test_edge_lengths(Hq, Hkv, D, interleaved):
+    """G in {1, 4, 7, 8, 16}; lengths straddling tile (16/32/64), page (256) and split boundaries."""
+    case = make_paged_case(len(LENS_EDGE), Hq, Hkv, D, LENS_EDGE, seed=Hq * 3 + D + int(interleaved))
+    check(case, interleaved=interleaved)
+
+
+@pytest.mark.parametrize("num_splits", [1, 2, 3, 4, 7, 8, 16, 33])
+def test_split_counts(num_splits):
+    lens = [4095, 3000, 257, 5, 0, 2047, 2048, 1023]
+    case = make_paged_case(8, 32, 8, 128, lens, seed=num_splits)
+    check(case, num_splits=num_splits)
+
+
+@pytest.mark.parametrize("D,variants", [(128, [1, 2, 3, 4, 5, 6, 7, 8]), (64, [1, 2, 3])])
+def test_all_kernel_variants(D, variants):
+    lens = [700, 255, 256, 31, 4000, 1, 0, 513]
+    Hq, Hkv = (32, 8) if D == 128 else (14, 2)
+    for v in variants:
+        case = make_paged_case(8, Hq, Hkv, D, lens, seed=10 + v)
+        check(case, variant=v, num_splits=3)
+
+
+def test_head_groups_over_16():
+    """G = 32 > 16 query heads per KV head: two head groups re-stream the KV head."""
+    case = make_paged_case(3, 32, 1, 64, [300, 17, 1025], seed=4)
+    check(case)
+
+
+def test_unused_table_entries_and_wide_table():
+    """-1 in unused entries, table much wider than any sequence, garbage past the end of the sequence."""
+    case = make_paged_case(4, 32, 8, 128, [100, 600, 0, 255], seed=5, table_width=64)
+    assert int(case["table"].min()) == -1
+    check(case)
+
+
+def test_duplicate_rows_are_benign():
+    """scheduler.py:88-92 pads decode batches by duplicating sequences: several CTAs write the same
+    bytes to the same slot.  All copies must produce the same result."""
+    case = make_paged_case(6, 32, 8, 128, [300, 511, 40, 0, 0, 0], seed=6, duplicates={3: 0, 4: 1, 5: 0})
+    got = check(case)
+    assert torch.equal(got[3], got[0]) and torch.equal(got[5], got[0]) and torch.equal(got[4], got[1])
+
+
+def test_no_append_and_no_rotary():
+    case = make_paged_case(5, 32, 8, 128, [1, 256, 300, 1024, 77], seed=7)
+    got, want, d, kc_ref, vc_ref = run_both(case, append=False)
+    assert_close(got, want)
+    assert torch.equal(d["k_cache"].cpu(), case["k_cache"]) and torch.equal(d["v_cache"].cpu(), case["v_cache"])
+    case = make_paged_case(5, 32, 8, 128, [1, 256, 300, 1024, 77], seed=8)
+    check(case, rotary=False)
+
+
+def test_partial_rotary_dim():
+    case = make_paged_case(4, 8, 2, 128, [10, 300, 255, 64], seed=9)
+    case["cos"], case["sin"] = case["cos"][:, :32].contiguous(), case["sin"][:, :32].contiguous()   # rotary_dim 64 < D
+    check(case, interleaved=False)
+    case = make_paged_case(4, 8, 2, 128, [10, 300, 255, 64], seed=9)
+    case["cos"], case["sin"] = case["cos"][:, :16].contiguous(), case["sin"][:, :16].contiguous()   # rotary_dim 32
+    check(case, interleaved=True)
+
+
+def test_engine_style_slot_255_gap():
+    """The reference's off-by-one pair: position P is never written, attention
+    still runs over it with whatever the page holds (zeros in a fresh pool)."""
+    case = make_paged_case(2, 14, 2, 64, [129, 200], seed=11, fill="zeros")
+    g = torch.Generator().manual_seed(12)
+    for b, n in enumerate([128, 199]):                       # prompt tokens 0..n-1 present, position n skipped
+        blk = int(case["table"][b, 0])
+        case["k_cache"][blk, :n] = torch.randn(n, 2, 64, generator=g).to(torch.bfloat16)
+        case["v_cache"][blk, :n] = torch.randn(n, 2, 64, generator=g).to(torch.bfloat16)
+    check(case)
+
+
+def test_flash_attn_surface_and_strided_qkv():
+    """The reference call site: q/k/v are views of one [bs, 3*H*D] buffer (model_graph.py:152),
+    keyword surface of flash_attn_with_kvcache, [B, 1, H, D] in and out."""
+    B, H, D = 8, 16, 128
+    case = make_paged_case(B, H, H, D, [5, 255, 256, 700, 0, 1, 64, 2000], seed=13)
+    qkv = torch.stack((case["q"][:, 0], case["k"][:, 0], case["v"][:, 0]), dim=1).reshape(B, 3 * H * D)
+    d = to_dev(case)
+    q, k, v = qkv.cuda().reshape(B, 3, H, D).unbind(dim=1)
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(case["q"], kc_ref, vc_ref, case["k"], case["v"], case["cos"], case["sin"],
+                                  case["seqlens"], case["table"], None, True, False)
+    out = flash_attn_with_kvcache(q=q.unsqueeze(1), k_cache=d["k_cache"], v_cache=d["v_cache"],
+                                  k=k.unsqueeze(1), v=v.unsqueeze(1), rotary_cos=d["cos"], rotary_sin=d["sin"],
+                                  cache_seqlens=d["seqlens"], block_table=d["table"], causal=True,
+                                  window_size=(-1, -1), rotary_interleaved=False, alibi_slopes=None,
+                                  num_splits=max(1, 32 // max(1, B * 4)))
+    assert out.shape == (B, 1, H, D)
+    assert_close(out, want)
+    assert torch.equal(d["v_cache"].cpu(), vc_ref)
+    out2, lse = flash_attn_with_kvcache(q=q.unsqueeze(1), k_cache=d["k_cache"], v_cache=d["v_cache"],
+                                        cache_seqlens=d["seqlens"] + 1, block_table=d["table"], causal=True,
+                                        return_softmax_lse=True)
+    want2, lse_ref = paged_attention_oracle(case["q"], kc_ref, vc_ref, None, None, None, None,
+                                            case["seqlens"] + 1, case["table"], None, True, False, return_lse=True)
+    assert_close(out2, want2)
+    assert lse.shape == (B, H, 1)
+    assert torch.allclose(lse.cpu(), lse_ref, atol=2e-3, rtol=1e-3)
+    for bad in (dict(alibi_slopes=torch.zeros(H)), dict(window_size=(128, 0)), dict(softcap=1.0)):
+        with pytest.raises(NotImplementedError):
+            flash_attn_with_kvcache(q=q.unsqueeze(1), k_cache=d["k_cache"], v_cache=d["v_cache"],
+                                    cache_seqlens=d["seqlens"], block_table=d["table"], **bad)
+    old = pa.SPLIT_POLICY
+    try:
+        pa.SPLIT_POLICY = "exact"
+        out3 = flash_attn_with_kvcache(q=q.unsqueeze(1), k_cache=d["k_cache"], v_cache=d["v_cache"],
+                                       cache_seqlens=d["seqlens"] + 1, block_table=d["table"], num_splits=5)
+        assert_close(out3, want2)
+    finally:
+        pa.SPLIT_POLICY = old
+
+
+def test_paged_attention_class_api():
+    """PagedAttention.forward (paged_attention.py:216-267): metadata comes from the cache manager's
+    static buffers; rotary defaults to interleaved like the reference's class path."""
+    from core.cache_manager import KVCacheManager
+    from core.paged_attention import PagedAttention
+    Hq, Hkv, D, B = 32, 8, 128, 3
+    m = KVCacheManager(12, 256, 2, Hkv, D, dtype=torch.bfloat16, device="cuda", max_tokens=1024, max_batch_size=4)
+    att = PagedAttention(Hq, D, Hkv, device="cuda", max_batch_size=4)
+    assert att._cos_pool.shape == (8192, 64) and att._cos_pool.dtype == torch.bfloat16 and att.max_blocks == 32
+    lens = [100, 300, 255]
+    g = torch.Generator().manual_seed(14)
+    for sid, n in enumerate(lens):
+        ok, slots = m.alloc(sid, n)
+        m.put(sid, torch.randn(n, Hkv, D, generator=g).to(torch.bfloat16).cuda(),
+              torch.randn(n, Hkv, D, generator=g).to(torch.bfloat16).cuda(), 1, slots)
+    for sid in range(B):
+        m.append(sid)
+    bt, sl = m.cache_batch_data([0, 1, 2], lens)
+    q = torch.randn(B, Hq, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(B, Hkv, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, Hkv, D, generator=g).to(torch.bfloat16)
+    kc_ref, vc_ref = m.k_caches[1].cpu().clone(), m.v_caches[1].cpu().clone()
+    want = paged_attention_oracle(q[:, None], kc_ref, vc_ref, k[:, None], v[:, None], att._cos_pool.cpu(),
+                                  att._sin_pool.cpu(), sl.cpu(), bt.cpu(), att.scale, True, interleaved=True)
+    out = att.forward(q.cuda(), m, [0, 1, 2], lens, 1, key=k.cuda(), value=v.cuda())
+    assert out.shape == (B, Hq, D)
+    assert_close(out, want[:, 0])
+    assert torch.equal(m.v_caches[1].cpu(), vc_ref)
+    assert float(m.k_caches[0].abs().sum()) == 0.0          # other layers untouched
+
+
+def test_lse_combine_standalone():
+    B, H, S, D = 3, 5, 7, 128
+    g = torch.Generator().manual_seed(15)
+    o = torch.randn(B, H, S, D, generator=g)
+    lse = torch.randn(B, H, S, generator=g) * 3
+    lse[0, 0, :] = float("-inf")
+    lse[1, 2, 3:] = float("-inf")
+    w = torch.softmax(lse, dim=-1).nan_to_num(0.0)
+    want = (w[..., None] * o).sum(2)
+    lse_out = torch.empty(B, H, dtype=torch.float32, device="cuda")
+    got = b200ops.lse_combine(o.cuda(), lse.cuda(), lse_out=lse_out)
+    assert_close(got, want)
+    ref_lse = torch.logsumexp(lse, dim=-1)
+    assert torch.allclose(lse_out.cpu(), ref_lse, atol=1e-4, rtol=1e-4)
+
+
+def test_full_size_properties_llama3_8b_b32_4k():
+    """BASELINE.json configs[1] at full size: size-independent properties + oracle on a row subset."""
+    B, Hq, Hkv, D, ctx = 32, 32, 8, 128, 4095
+    case = make_paged_case(B, Hq, Hkv, D, [ctx] * B, seed=16, extra_blocks=5)
+    d = to_dev(case)
+    kc0, vc0 = d["k_cache"].clone(), d["v_cache"].clone()
+
+    def run(kc, vc, table, **kw):
+        return b200ops.paged_attn_decode(d["q"][:, 0], kc, vc, d["k"][:, 0], d["v"][:, 0], d["cos"], d["sin"],
+                                         d["seqlens"], table, softmax_scale=case["scale"], **kw)
+    base = run(d["k_cache"], d["v_cache"], d["table"])
+    # (1) oracle on 3 of the 32 rows
+    rows = [0, 13, 31]
+    sub = {k: (v[rows] if k in ("q", "k", "v", "seqlens", "table") else v) for k, v in case.items()}
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(sub["q"], kc_ref, vc_ref, sub["k"], sub["v"], case["cos"], case["sin"],
+                                  sub["seqlens"], sub["table"], case["scale"], True, False)
+    assert_close(base[rows], want[:, 0])
+    # (2) appended rows: V bit-exact at exactly the slots block_table names
+    for b in rows:
+        blk, off = int(case["table"][b, ctx // 256]), ctx % 256
+        assert torch.equal(d["v_cache"][blk, off].cpu(), case["v"][b, 0])
+    changed = (d["v_cache"] != vc0).any(dim=-1).any(dim=-1)
+    assert int(changed.sum()) <= B, "only one slot per sequence may change"
+    # (3) idempotence: running again on the updated cache gives bit-identical output and cache
+    kc1, vc1 = d["k_cache"].clone(), d["v_cache"].clone()
+    again = run(d["k_cache"], d["v_cache"], d["table"])
+    assert torch.equal(again, base) and torch.equal(d["k_cache"], kc1) and torch.equal(d["v_cache"], vc1)
+    # (4) linearity in V: scaling V (cache and new row) by 2 scales the output by exactly 2
+    vc2 = (vc0.float() * 2).to(torch.bfloat16)
+    kc2 = kc0.clone()
+    dbl = b200ops.paged_attn_decode(d["q"][:, 0], kc2, vc2, d["k"][:, 0], (d["v"][:, 0].float() * 2).to(torch.bfloat16),
+                                    d["cos"], d["sin"], d["seqlens"], d["table"], softmax_scale=case["scale"])
+    assert torch.equal(dbl.float(), base.float() * 2)
+    # (5) page-indirection invariance: permuting physical pages (and the table with them) changes nothing
+    n_blocks = kc0.shape[0]
+    perm = torch.randperm(n_blocks, generator=torch.Generator().manual_seed(17)).cuda()
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(n_blocks, device="cuda")
+    kc3, vc3 = kc0[perm].contiguous(), vc0[perm].contiguous()
+    table3 = torch.where(d["table"] >= 0, inv[d["table"].clamp(min=0).long()].int(), d["table"])
+    moved = run(kc3, vc3, table3)
+    assert torch.equal(moved, base)
+    # (6) split invariance within tolerance, and explicit single split
+    one = run(kc0.clone(), vc0.clone(), d["table"], num_splits=1)
+    many = run(kc0.clone(), vc0.clone(), d["table"], num_splits=16)
+    assert_close(one, base.float())
+    assert_close(many, base.float())
+
+
+def test_long_context_split_kv_128k():
+    """BASELINE.json configs[4] shape at reduced batch: 128k context, 512 pages per sequence."""
+    B, Hq, Hkv, D, ctx = 2, 32, 8, 128, 131071
+    case = make_paged_case(B, Hq, Hkv, D, [ctx, 100000], seed=18, rot_rows=131073)
+    check(case)
+
+
+def test_cuda_graph_capture_and_replay():
+    """ModelGraphRunner contract (model_graph.py:240-250): the op is capturable, and a replay picks
+    up NEW cache_seqlens / block_table contents from the same device buffers."""
+    B, Hq, Hkv, D = 8, 32, 8, 128
+    case_a = make_paged_case(B, Hq, Hkv, D, [10, 300, 254, 256, 1000, 0, 77, 512], seed=19, table_width=8)
+    d = to_dev(case_a)
+    out = torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda")
+    args = (d["q"][:, 0], d["k_cache"], d["v_cache"], d["k"][:, 0], d["v"][:, 0], d["cos"], d["sin"], d["seqlens"], d["table"])
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            b200ops.paged_attn_decode(*args, softmax_scale=case_a["scale"], out=out)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    d["k_cache"].copy_(case_a["k_cache"]); d["v_cache"].copy_(case_a["v_cache"])
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        b200ops.paged_attn_decode(*args, softmax_scale=case_a["scale"], out=out)
+    d["k_cache"].copy_(case_a["k_cache"]); d["v_cache"].copy_(case_a["v_cache"])
+    g.replay()
+    torch.cuda.synchronize()
+    kc_ref, vc_ref = case_a["k_cache"].clone(), case_a["v_cache"].clone()
+    want = paged_attention_oracle(case_a["q"], kc_ref, vc_ref, case_a["k"], case_a["v"], case_a["cos"], case_a["sin"],
+                                  case_a["seqlens"], case_a["table"], case_a["scale"], True, False)
+    assert_close(out, want[:, 0])
+    assert torch.equal(d["v_cache"].cpu(), vc_ref)
+    # second step: lengths advance by one, a new q/k/v arrives in the SAME buffers
+    g2 = torch.Generator().manual_seed(20)
+    q2 = torch.randn(B, 1, Hq, D, generator=g2).to(torch.bfloat16)
+    k2 = torch.randn(B, 1, Hkv, D, generator=g2).to(torch.bfloat16)
+    v2 = torch.randn(B, 1, Hkv, D, generator=g2).to(torch.bfloat16)
+    d["q"].copy_(q2); d["k"].copy_(k2); d["v"].copy_(v2)
+    d["seqlens"].add_(1)
+    g.replay()
+    torch.cuda.synchronize()
+    want2 = paged_attention_oracle(q2, kc_ref, vc_ref, k2, v2, case_a["cos"], case_a["sin"],
+                                   case_a["seqlens"] + 1, case_a["table"], case_a["scale"], True, False)
+    assert_close(out, want2[:, 0])
+    assert torch.equal(d["v_cache"].cpu(), vc_ref)

@@ -1,0 +1,150 @@
+"""sm_100a elementwise / row kernels against the fp32 restatement of the Triton bodies
+(<= 1 bf16 ulp); store_kvcache bit-exact.  Called through the
+reference-named Python operators, i.e. through the C-ABI."""
+import pytest
+import torch
+
+from oracle.elementwise import bf16_ulp_diff, rmsnorm_oracle, rmsnorm_residual_oracle, swiglu_oracle
+from oracle.paged_attention import store_kvcache_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _ulp_ok(got, want, max_ulp=1, frac_exact=0.98):
+    d = bf16_ulp_diff(got.cpu(), want.cpu())
+    assert int(d.max()) <= max_ulp, f"max ulp diff {int(d.max())}"
+    assert float((d == 0).float().mean()) >= frac_exact, f"only {float((d == 0).float().mean()):.4f} bit-exact"
+
+
+@pytest.mark.parametrize("rows,d", [(1, 14336), (32, 14336), (64, 3584), (7, 4864), (3, 100), (2048, 1024), (5, 8)])
+def test_swiglu(rows, d):
+    from kernel.swiglu import swiglu_fused, swiglu_gemm
+    g = torch.Generator().manual_seed(rows * 131 + d)
+    gu = (torch.randn(rows, 2 * d, generator=g) * 2).to(torch.bfloat16)
+    want = swiglu_oracle(gu)
+    got = swiglu_fused(gu.cuda())
+    assert got.shape == (rows, d) and got.dtype == torch.bfloat16
+    _ulp_ok(got, want)
+    buf = torch.empty(rows, d, dtype=torch.bfloat16, device="cuda")
+    ret = swiglu_gemm(gu.cuda(), buf)
+    assert ret.data_ptr() == buf.data_ptr()
+    assert torch.equal(buf, got)
+    got3 = swiglu_fused(gu.cuda().view(1, rows, 2 * d))
+    assert got3.shape == (1, rows, d) and torch.equal(got3[0], got)
+
+
+def test_swiglu_asserts():
+    from kernel.swiglu import swiglu_gemm
+    gu = torch.zeros(2, 16, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(AssertionError):
+        swiglu_gemm(gu, torch.zeros(2, 8, dtype=torch.float16, device="cuda"))
+    with pytest.raises(AssertionError):
+        swiglu_gemm(gu, torch.zeros(2, 4, dtype=torch.bfloat16, device="cuda"))
+
+
+@pytest.mark.parametrize("rows,n", [(1, 4096), (32, 4096), (64, 8192), (5, 896), (3, 3584), (1024, 4096),
+                                     (600, 896), (2, 100), (4, 16384), (2, 70000)])
+@pytest.mark.parametrize("wdt", [torch.bfloat16, torch.float32])
+def test_rmsnorm(rows, n, wdt):
+    from kernel.rmsnorm_add import rmsnorm, rmsnorm_
+    g = torch.Generator().manual_seed(rows * 7 + n)
+    x = (torch.randn(rows, n, generator=g) * 3).to(torch.bfloat16)
+    w = (1 + 0.2 * torch.randn(n, generator=g)).to(wdt)
+    want = rmsnorm_oracle(x, w, 1e-6)
+    got = rmsnorm(x.cuda(), w.cuda(), 1e-6)
+    _ulp_ok(got, want)
+    buf = torch.empty_like(got)
+    assert rmsnorm_(x.cuda(), w.cuda(), buf, 1e-6).data_ptr() == buf.data_ptr()
+    assert torch.equal(buf, got)
+
+
+def test_rmsnorm_strided_rows_and_3d():
+    from kernel.rmsnorm_add import rmsnorm_
+    g = torch.Generator().manual_seed(3)
+    big = (torch.randn(6, 2 * 1024, generator=g)).to(torch.bfloat16).cuda()
+    x = big[:, :1024]                                    # row stride 2048, last dim contiguous
+    w = torch.ones(1024, dtype=torch.bfloat16, device="cuda")
+    out = torch.empty(6, 1024, dtype=torch.bfloat16, device="cuda")
+    rmsnorm_(x, w, out, 1e-5)
+    _ulp_ok(out, rmsnorm_oracle(x.cpu(), w.cpu(), 1e-5))
+
+
+@pytest.mark.parametrize("rows,n", [(1, 4096), (32, 4096), (64, 8192), (5, 896), (3, 3584), (2048, 4096), (2, 100)])
+def test_rmsnorm_residual(rows, n):
+    from kernel.rmsnorm_residual import rmsnorm_residual_fused, rmsnorm_residual_gemm, rmsnorm_residual_hybrid
+    g = torch.Generator().manual_seed(rows * 11 + n)
+    x = (torch.randn(rows, n, generator=g) * 2).to(torch.bfloat16)
+    r = (torch.randn(rows, n, generator=g) * 2).to(torch.bfloat16)
+    w = (1 + 0.2 * torch.randn(n, generator=g)).to(torch.bfloat16)
+    want_y, want_res = rmsnorm_residual_oracle(x, r, w, 1e-6)
+    y, res = rmsnorm_residual_fused(x.cuda(), r.cuda(), w.cuda(), 1e-6)
+    assert torch.equal(res.cpu(), want_res), "residual output must be the bit-exact bf16(x + r)"
+    _ulp_ok(y, want_y)
+    yb, rb = torch.empty_like(y), torch.empty_like(y)
+    o1, o2 = rmsnorm_residual_gemm(x.cuda(), r.cuda(), w.cuda(), yb, rb, 1e-6)
+    assert o1.data_ptr() == yb.data_ptr() and o2.data_ptr() == rb.data_ptr()
+    assert torch.equal(yb, y) and torch.equal(rb, res)
+    yh = torch.empty_like(y)
+    o1, o2 = rmsnorm_residual_hybrid(x.cuda(), r.cuda(), w.cuda(), yh, 1e-6)
+    assert torch.equal(o1, y) and torch.equal(o2, res)
+
+
+def test_rmsnorm_residual_in_place_residual():
+    """model_graph.py:213-216 style aliasing: the residual output may alias the residual input."""
+    from kernel.rmsnorm_residual import rmsnorm_residual_gemm
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(8, 4096, generator=g).to(torch.bfloat16)
+    r = torch.randn(8, 4096, generator=g).to(torch.bfloat16)
+    w = torch.ones(4096, dtype=torch.bfloat16)
+    want_y, want_res = rmsnorm_residual_oracle(x, r, w, 1e-6)
+    rc = r.cuda()
+    y = torch.empty(8, 4096, dtype=torch.bfloat16, device="cuda")
+    rmsnorm_residual_gemm(x.cuda(), rc, w.cuda(), y, rc, 1e-6)
+    assert torch.equal(rc.cpu(), want_res)
+    _ulp_ok(y, want_y)
+
+
+@pytest.mark.parametrize("T,H,D,page", [(9, 2, 16, 4), (300, 8, 128, 256), (64, 2, 64, 256), (5, 3, 20, 16)])
+def test_store_kvcache_bit_exact(T, H, D, page):
+    from core.cache_manager import store_kvcache, store_kvcache_batch
+    g = torch.Generator().manual_seed(T)
+    n_blocks = -(-T // page) + 2
+    key = torch.randn(T, H, D, generator=g).to(torch.bfloat16)
+    val = torch.randn(T, H, D, generator=g).to(torch.bfloat16)
+    slots = torch.randperm(n_blocks * page, generator=g)[:T].to(torch.int32)
+    slots[::4] = -1
+    kc = torch.randn(n_blocks, page, H, D, generator=g).to(torch.bfloat16)
+    vc = torch.randn(n_blocks, page, H, D, generator=g).to(torch.bfloat16)
+    kc_d, vc_d = kc.cuda(), vc.cuda()
+    store_kvcache_oracle(key, val, kc, vc, slots, page)
+    store_kvcache(key.cuda(), val.cuda(), kc_d, vc_d, slots.cuda(), page)
+    assert torch.equal(kc_d.cpu(), kc) and torch.equal(vc_d.cpu(), vc)
+    # strided key/value views (q/k/v slices of one qkv buffer) and the batch wrapper
+    qkv = torch.randn(T, 3, H, D, generator=g).to(torch.bfloat16)
+    kc2, vc2 = kc.clone(), vc.clone()
+    store_kvcache_oracle(qkv[:, 1], qkv[:, 2], kc2, vc2, slots, page)
+    qkv_d = qkv.cuda()
+    if D % 8 == 0:
+        store_kvcache_batch(qkv_d[:, 1].unsqueeze(1), qkv_d[:, 2].unsqueeze(1), kc_d, vc_d,
+                            slots.cuda().view(T, 1), page)
+    else:
+        store_kvcache(qkv_d[:, 1], qkv_d[:, 2], kc_d, vc_d, slots.cuda(), page)
+    assert torch.equal(kc_d.cpu(), kc2) and torch.equal(vc_d.cpu(), vc2)
+
+
+def test_cache_manager_put_on_device():
+    from core.cache_manager import KVCacheManager
+    m = KVCacheManager(4, 256, 2, 2, 64, dtype=torch.bfloat16, device="cuda", max_tokens=1024, max_batch_size=4)
+    ok, slots = m.alloc(7, 300)
+    assert ok and slots.is_cuda and slots.dtype == torch.int32
+    g = torch.Generator().manual_seed(1)
+    key = torch.randn(300, 2, 64, generator=g).to(torch.bfloat16).cuda()
+    val = torch.randn(300, 2, 64, generator=g).to(torch.bfloat16).cuda()
+    m.put(7, key, val, 1, slots)
+    k, v = m.get(1)
+    blocks = m.get_blocks(7)
+    assert torch.equal(k[blocks[0]], key[:256]) and torch.equal(v[blocks[1], :44], val[256:])
+    assert float(m.k_caches[0].abs().sum()) == 0.0
+    bt, sl = m.cache_batch_data([7, 7], [300, 300])
+    torch.cuda.synchronize()
+    assert bt.is_cuda and bt.tolist() == [blocks + [-1, -1], blocks + [-1, -1]] and sl.tolist() == [300, 300]

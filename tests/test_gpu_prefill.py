@@ -1,0 +1,100 @@
+"""Paged prefill attention (fused RoPE + page scatter + tcgen05/TMEM causal attention) against
+the fp32 oracle, through the reference-named operator surface."""
+import pytest
+import torch
+
+import b200ops
+from core.paged_attention import flash_attn_with_kvcache
+from oracle.elementwise import bf16_ulp_diff
+from oracle.paged_attention import paged_attention_oracle
+from oracle.rotary import rope_eager_oracle
+from _cases import assert_close, make_paged_case, to_dev
+
+pytestmark = pytest.mark.gpu
+
+
+def check_prefill(case, interleaved=False, causal=True, rotary=True):
+    d = to_dev(case)
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(case["q"], kc_ref, vc_ref, case["k"], case["v"],
+                                  case["cos"] if rotary else None, case["sin"] if rotary else None,
+                                  case["seqlens"], case["table"], case["scale"], causal=causal, interleaved=interleaved)
+    got = b200ops.paged_attn_prefill(d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"],
+                                     d["cos"] if rotary else None, d["sin"] if rotary else None,
+                                     d["seqlens"], d["table"], softmax_scale=case["scale"], causal=causal,
+                                     rotary_interleaved=interleaved)
+    torch.cuda.synchronize()
+    assert torch.equal(d["v_cache"].cpu(), vc_ref), "V pages must be bit-exact"
+    kd = d["k_cache"].cpu()
+    assert int(bf16_ulp_diff(kd, kc_ref).max()) <= 1, "rotated K pages differ by more than 1 bf16 ulp"
+    assert_close(got, want, what="prefill attention output")
+    return got
+
+
+@pytest.mark.parametrize("B,S,Hq,Hkv,D", [(1, 128, 4, 4, 128), (2, 128, 8, 2, 128), (1, 256, 4, 1, 128),
+                                           (2, 100, 4, 2, 128), (1, 1, 4, 4, 128), (3, 129, 14, 2, 64),
+                                           (1, 512, 28, 4, 128), (2, 300, 32, 8, 128)])
+def test_prefill_from_empty_cache(B, S, Hq, Hkv, D):
+    """The reference's prefill: cache_seqlens zeroed (model_prefill.py:32), positions 0..S-1."""
+    case = make_paged_case(B, Hq, Hkv, D, [0] * B, S_new=S, seed=S + Hq)
+    check_prefill(case)
+
+
+@pytest.mark.parametrize("prefix,S", [(1, 127), (255, 2), (256, 128), (300, 200), (1000, 64), (129, 513)])
+def test_chunked_prefill_on_cached_prefix(prefix, S):
+    """configs[2]: a chunk of S new tokens on top of a cached prefix (bottom-right causal mask)."""
+    case = make_paged_case(2, 8, 2, 128, [prefix, max(0, prefix - 77)], S_new=S, seed=prefix + S)
+    check_prefill(case)
+
+
+def test_prefill_interleaved_and_noncausal():
+    case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=3)
+    check_prefill(case, interleaved=True)
+    case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=4)
+    check_prefill(case, causal=False)
+
+
+def test_reference_call_site_prerotated_inputs():
+    """model_prefill.py:45-52: q/k rotated by the eager bf16 RoPE first, then
+    flash_attn_with_kvcache(q, k_cache, v_cache, k=k, v=v, cache_seqlens=0, block_table, causal=True)
+    with NO rotary tables; q/k/v are strided views of one qkv tensor."""
+    B, S, H, D = 2, 192, 8, 128
+    case = make_paged_case(B, H, H, D, [0, 0], S_new=S, seed=5)
+    qkv = torch.stack((case["q"], case["k"], case["v"]), dim=2)            # [B, S, 3, H, D]
+    q, k, v = qkv.unbind(dim=2)
+    q_rot, k_rot = rope_eager_oracle(q, k, case["cos"], case["sin"])
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(q_rot, kc_ref, vc_ref, k_rot, v, None, None, case["seqlens"], case["table"],
+                                  None, True, False)
+    d = to_dev(case)
+    qkv_d = qkv.cuda()
+    qd, kd, vd = qkv_d.unbind(dim=2)
+    from core.layer.rope import RoPE
+    qd, kd = RoPE().forward(qd, kd, d["cos"], d["sin"])
+    assert torch.equal(qd.cpu(), q_rot) or int(bf16_ulp_diff(qd.cpu(), q_rot).max()) <= 1
+    out = flash_attn_with_kvcache(q=qd, k_cache=d["k_cache"], v_cache=d["v_cache"], k=kd, v=vd,
+                                  cache_seqlens=d["seqlens"], block_table=d["table"], causal=True)
+    assert out.shape == (B, S, H, D)
+    assert_close(out, want)
+    assert torch.equal(d["v_cache"].cpu(), vc_ref)
+
+
+def test_prefill_then_decode_consistency():
+    """encode -> decode round trip: decoding token S on top of a prefilled cache equals the last
+    row of prefilling S + 1 tokens at once (same K/V bytes in the pages, same attention)."""
+    B, S, Hq, Hkv, D = 2, 200, 32, 8, 128
+    case = make_paged_case(B, Hq, Hkv, D, [0, 0], S_new=S + 1, seed=6, fill="zeros")
+    d = to_dev(case)
+    full = b200ops.paged_attn_prefill(d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"], d["cos"], d["sin"],
+                                      d["seqlens"], d["table"], softmax_scale=case["scale"])
+    pages_k, pages_v = d["k_cache"].clone(), d["v_cache"].clone()
+    d2 = to_dev(case)
+    b200ops.paged_attn_prefill(d2["q"][:, :S].contiguous(), d2["k"][:, :S].contiguous(), d2["v"][:, :S].contiguous(),
+                               d2["k_cache"], d2["v_cache"], d2["cos"], d2["sin"], d2["seqlens"], d2["table"],
+                               softmax_scale=case["scale"])
+    lens = torch.full((B,), S, dtype=torch.int32, device="cuda")
+    last = b200ops.paged_attn_decode(d2["q"][:, S], d2["k_cache"], d2["v_cache"], d2["k"][:, S], d2["v"][:, S],
+                                     d2["cos"], d2["sin"], lens, d2["table"], softmax_scale=case["scale"])
+    assert torch.equal(d2["v_cache"], pages_v), "prefill(S) + decode must leave the same V pages as prefill(S+1)"
+    assert torch.equal(d2["k_cache"], pages_k), "rotated K written by the decode kernel and the prefill kernel must be bit-identical"
+    assert_close(last, full[:, S].float(), what="decode vs last prefill row")
