@@ -115,8 +115,9 @@ int b200_store_kvcache(const void* key, const void* value,
  * cos/sin may be NULL (no rotary).
  *
  * Workspace (caller-owned, sized by b200_decode_workspace_bytes, zeroed ONCE
- * by the caller before first use; the kernel leaves it reusable):
- *   [ counters | lse partials | O partials ]
+ * by the caller before first use; the kernel leaves it reusable, also by
+ * launches of other shapes):
+ *   [ 65536 arrival counters (fixed) | lse partials | O partials ]
  * ------------------------------------------------------------------------ */
 typedef struct b200_decode_args {
     const void* q;            /* [B, Hq, D] bf16                                  */

@@ -111,15 +111,20 @@ def sm_count(device: torch.device) -> int:
     return _SM_COUNT[idx]
 
 
-def decode_num_splits(batch: int, kv_heads: int, capacity_tokens: int, n_sm: int = 148,
-                      tokens_per_cta_chunk: int = 64, ctas_per_sm: int = 2, waves: int = 4) -> int:
-    """Split count from launch-time constants only (CUDA-graph capture fixes the grid;
-    model_graph.py:167 passes max(1, 32 // (4*bs)), which leaves 256 CTAs for 148 SMs at
-    bs=32).  Aim for `waves` full waves of CTAs; never more splits than the block table
-    could ever give work to."""
+def decode_num_splits(batch: int, kv_heads: int, capacity_tokens: int, n_sm: int = 148) -> int:
+    """Split count from launch-time constants only (CUDA-graph capture fixes the grid).
+
+    Measured on B200 (profiles/r01/tune_*.json): one CTA per (sequence, kv head) saturates HBM
+    as soon as there are at least as many CTAs as SMs, every extra split costs a prologue and a
+    partial merge, and a grid that spills into a second partial wave loses more than it gains.
+    So: no split when batch * kv_heads >= #SMs; otherwise the largest split count that keeps the
+    grid within ~1.75 CTAs per SM (one wave), and never less than 256 tokens per split of what
+    the block table can hold."""
     base = max(1, batch * kv_heads)
-    want = -(-n_sm * ctas_per_sm * waves // base)
-    cap = max(1, capacity_tokens // tokens_per_cta_chunk)
+    if base >= n_sm:
+        return 1
+    want = max(1, int(1.75 * n_sm) // base)
+    cap = max(1, capacity_tokens // 256)
     return int(max(1, min(want, cap, 128)))
 
 

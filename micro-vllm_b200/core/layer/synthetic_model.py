@@ -51,22 +51,28 @@ class RMSNormModule(nn.Module):
         return rmsnorm(x, self.weight, self.eps)
 
 
-def _linear(i, o, bias, dtype, device, gen, std):
+def _randn(shape, gen, device, fast):
+    if fast:                                   # device-side generator: seconds instead of minutes for 70B-shaped layers
+        return torch.randn(*shape, generator=gen, device=device, dtype=torch.float32)
+    return torch.randn(*shape, generator=gen, dtype=torch.float32)
+
+
+def _linear(i, o, bias, dtype, device, gen, std, fast=False):
     lin = nn.Linear(i, o, bias=bias, dtype=dtype, device=device)
     with torch.no_grad():
-        lin.weight.copy_((torch.randn(o, i, generator=gen, dtype=torch.float32) * std).to(dtype))
+        lin.weight.copy_((_randn((o, i), gen, device, fast) * std).to(dtype))
         if bias:
-            lin.bias.copy_((torch.randn(o, generator=gen, dtype=torch.float32) * std).to(dtype))
+            lin.bias.copy_((_randn((o,), gen, device, fast) * std).to(dtype))
     lin.requires_grad_(False)
     return lin
 
 
 def build_synthetic_model(shape: Shape, n_layers: int | None = None, device="cuda", dtype=torch.bfloat16,
                           seed: int = 0, std: float = 0.02, vocab: int | None = None,
-                          norm_weight_jitter: float = 0.1):
-    """Deterministic (CPU generator) random-init tree; the same seed gives bit-identical weights
-    on every rank and on the CPU oracle side."""
-    gen = torch.Generator().manual_seed(seed)
+                          norm_weight_jitter: float = 0.1, fast_init: bool = False):
+    """Deterministic random-init tree; the same seed gives bit-identical weights on every rank
+    (CPU generator by default; ``fast_init`` draws on the device for the big bench shapes)."""
+    gen = (torch.Generator(device=device) if fast_init else torch.Generator()).manual_seed(seed)
     L = n_layers if n_layers is not None else shape.layers
     V = vocab if vocab is not None else shape.vocab
     H, D = shape.hidden, shape.head_dim
@@ -78,7 +84,7 @@ def build_synthetic_model(shape: Shape, n_layers: int | None = None, device="cud
     tr = nn.Module()
     tr.wte = nn.Embedding(V, H, dtype=dtype, device=device)
     with torch.no_grad():
-        tr.wte.weight.copy_(torch.randn(V, H, generator=gen, dtype=torch.float32).to(dtype))
+        tr.wte.weight.copy_(_randn((V, H), gen, device, fast_init).to(dtype))
     tr.wte.requires_grad_(False)
     blocks = []
     for _ in range(L):
@@ -87,17 +93,17 @@ def build_synthetic_model(shape: Shape, n_layers: int | None = None, device="cud
         blk.ln_2 = RMSNormModule(H, shape.eps, dtype, device)
         with torch.no_grad():
             for ln in (blk.ln_1, blk.ln_2):
-                ln.weight.copy_((1.0 + norm_weight_jitter * torch.randn(H, generator=gen)).to(dtype))
+                ln.weight.copy_((1.0 + norm_weight_jitter * _randn((H,), gen, device, fast_init)).to(dtype))
         blk.attn = nn.Module()
-        blk.attn.c_attn = _linear(H, qkv_out, shape.qkv_bias, dtype, device, gen, std)
-        blk.attn.c_proj = _linear(shape.heads * D, H, False, dtype, device, gen, std)
+        blk.attn.c_attn = _linear(H, qkv_out, shape.qkv_bias, dtype, device, gen, std, fast_init)
+        blk.attn.c_proj = _linear(shape.heads * D, H, False, dtype, device, gen, std, fast_init)
         blk.mlp = nn.Module()
-        blk.mlp.w1 = _linear(H, shape.ffn, False, dtype, device, gen, std)       # up
-        blk.mlp.w2 = _linear(H, shape.ffn, False, dtype, device, gen, std)       # gate
-        blk.mlp.c_proj = _linear(shape.ffn, H, False, dtype, device, gen, std)
+        blk.mlp.w1 = _linear(H, shape.ffn, False, dtype, device, gen, std, fast_init)       # up
+        blk.mlp.w2 = _linear(H, shape.ffn, False, dtype, device, gen, std, fast_init)       # gate
+        blk.mlp.c_proj = _linear(shape.ffn, H, False, dtype, device, gen, std, fast_init)
         blocks.append(blk)
     tr.h = nn.ModuleList(blocks)
     tr.ln_f = RMSNormModule(H, shape.eps, dtype, device)
     model.transformer = tr
-    model.lm_head = _linear(H, V, False, dtype, device, gen, std)
+    model.lm_head = _linear(H, V, False, dtype, device, gen, std, fast_init)
     return model

@@ -382,18 +382,19 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     if (S == 1) return;
 
     // ---- split merge by the last-arriving CTA of this (b, kv head, group)
-    __threadfence();
     __syncthreads();
     if (tid == 0) {
+        // acq_rel at gpu scope: releases this CTA's partials (ordered before it by the barrier,
+        // fences are cumulative) and acquires the partials of every CTA that arrived earlier
         int32_t* ctr = p.counters + ((int64_t)b * gridDim.y + blockIdx.y);
-        const int prev = atomicAdd(ctr, 1);
+        int prev;
+        asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(prev) : "l"(ctr) : "memory");
         const int last = (prev == S - 1);
         if (last) *ctr = 0;                              // leave the counter reusable (graph replay)
         *s_flag = last;
     }
     __syncthreads();
     if (!*s_flag) return;
-    __threadfence();
 
     float* c_w = reinterpret_cast<float*>(smem);        // [gcount][S] merge weights
     for (int idx = tid; idx < gcount * S; idx += C::THREADS) {
@@ -466,11 +467,15 @@ lse_combine_kernel(const float* __restrict__ o_part, const float* __restrict__ l
 // ------------------------------------------------------------------ host side
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
+// Workspace layout: [ arrival counters (fixed capacity) | lse partials | O partials ].
+// The counter region has a FIXED size and position so that it stays all-zero across launches
+// of different shapes (every launch resets the counters it used); only the partials move.
+constexpr int64_t kMaxCounters = 65536;
 struct WsLayout { int64_t counters_off, lse_off, o_off, total; };
-static WsLayout ws_layout(int B, int Hq, int Hkv, int D, int S, int ngroups) {
+static WsLayout ws_layout(int B, int Hq, int D, int S) {
     WsLayout w;
     w.counters_off = 0;
-    w.lse_off = align_up((int64_t)B * Hkv * ngroups * 4, 256);
+    w.lse_off = kMaxCounters * 4;
     w.o_off = w.lse_off + align_up((int64_t)B * Hq * S * 4, 256);
     w.total = w.o_off + (int64_t)B * Hq * S * D * 4;
     return w;
@@ -499,9 +504,7 @@ using namespace b200;
 
 extern "C" int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D, int32_t num_splits) {
     if (B <= 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || num_splits <= 0 || Hq % Hkv != 0) return -1;
-    const int G = Hq / Hkv;
-    const int ngroups = (G + 15) / 16;
-    return ws_layout(B, Hq, Hkv, D, num_splits, ngroups).total;
+    return ws_layout(B, Hq, D, num_splits).total;
 }
 
 extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
@@ -535,7 +538,10 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     const int S = a->num_splits;
     DecodeParams p;
     if (S > 1) {
-        const WsLayout w = ws_layout(a->B, a->Hq, a->Hkv, a->D, S, ngroups);
+        if ((int64_t)a->B * a->Hkv * ngroups > kMaxCounters)
+            B200_FAIL(B200_E_RANGE, "decode: B * Hkv * groups = %lld exceeds the %lld split-merge counters",
+                      (long long)a->B * a->Hkv * ngroups, (long long)kMaxCounters);
+        const WsLayout w = ws_layout(a->B, a->Hq, a->D, S);
         if (!a->workspace || a->workspace_bytes < w.total)
             B200_FAIL(B200_E_RANGE, "decode: workspace %lld B < required %lld B", (long long)a->workspace_bytes, (long long)w.total);
         uint8_t* ws = (uint8_t*)a->workspace;
@@ -564,13 +570,13 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
 
     if (a->D == 128) {
         switch (a->variant) {
-            case 0:
             case 1: return launch_decode<DCfg<128, 4, 16, 3, 2>>(p, S, st);   //  96 KB, 2 CTA/SM
             case 2: return launch_decode<DCfg<128, 4, 16, 4, 1>>(p, S, st);   // 128 KB
             case 3: return launch_decode<DCfg<128, 4, 32, 3, 1>>(p, S, st);   // 192 KB
             case 4: return launch_decode<DCfg<128, 8, 16, 3, 1>>(p, S, st);   // 192 KB
             case 5: return launch_decode<DCfg<128, 2, 16, 4, 3>>(p, S, st);   //  64 KB, 3 CTA/SM
-            case 6: return launch_decode<DCfg<128, 4, 16, 2, 3>>(p, S, st);   //  64 KB, 3 CTA/SM
+            case 0:
+            case 6: return launch_decode<DCfg<128, 4, 16, 2, 3>>(p, S, st);   //  64 KB, 3 CTA/SM (default: best on the B200 sweep)
             case 7: return launch_decode<DCfg<128, 8, 16, 2, 1>>(p, S, st);   // 128 KB
             case 8: return launch_decode<DCfg<128, 2, 32, 3, 2>>(p, S, st);   //  96 KB, 2 CTA/SM
             default: B200_FAIL(B200_E_RANGE, "decode: unknown variant %d", a->variant);

@@ -23,7 +23,7 @@ CASES = {
     "decode_interleaved_mha_d64": (dict(B=4, Hq=4, Hkv=4, D=64, lens=[1, 254, 257, 40], seed=2), True, True),
     "decode_gqa7_d64": (dict(B=3, Hq=14, Hkv=2, D=64, lens=[129, 0, 255], seed=3), False, True),
     "decode_llama8b_b4_4k": (dict(B=4, Hq=32, Hkv=8, D=128, lens=[4095, 4000, 2049, 1], seed=6), False, True),
-    "prefill_empty_d128": (dict(B=2, Hq=8, Hkv=2, D=128, lens=[0, 0], S_new=150, seed=4), False, False),
+    "prefill_empty_d128": (dict(B=1, Hq=8, Hkv=2, D=128, lens=[0], S_new=150, seed=4), False, False),
     "prefill_prefix_d128": (dict(B=1, Hq=4, Hkv=1, D=128, lens=[200], S_new=130, seed=5), False, True),
 }
 

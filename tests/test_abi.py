@@ -59,7 +59,7 @@ def test_argument_errors_without_device():
     assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_SHAPE       # head_dim
     a.D, a.block_size, a.n_blocks, a.max_blocks_per_seq, a.num_splits = 128, 256, 4, 4, 0
     assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_RANGE       # num_splits
-    assert lib.b200_decode_workspace_bytes(32, 32, 8, 128, 4) > 32 * 32 * 4 * 128 * 4
+    assert lib.b200_decode_workspace_bytes(32, 32, 8, 128, 4) == 65536 * 4 + 32 * 32 * 4 * 4 + 32 * 32 * 4 * 128 * 4
     assert lib.b200_decode_workspace_bytes(32, 30, 8, 128, 4) == -1
     assert lib.b200_prefill_workspace_bytes(2, 128, 32, 128) == 2 * 128 * 32 * 128 * 2
 
@@ -85,7 +85,8 @@ def test_ops_refuse_cpu_tensors():
 
 def test_split_heuristic_is_launch_constant():
     from b200ops import decode_num_splits
-    assert decode_num_splits(32, 8, 16 * 256) == 5
-    assert decode_num_splits(1, 2, 4 * 256) == 16            # capped by what the table can hold
-    assert decode_num_splits(8, 8, 512 * 256) == 19
+    assert decode_num_splits(32, 8, 16 * 256) == 1           # 256 CTAs >= 148 SMs: no split
+    assert decode_num_splits(1, 2, 4 * 256) == 4             # capped by what the table can hold
+    assert decode_num_splits(8, 8, 512 * 256) == 4           # 256 CTAs, one wave
+    assert decode_num_splits(1, 8, 16 * 256) == 16
     assert decode_num_splits(64, 8, 32 * 256) >= 1

@@ -73,6 +73,17 @@ def test_all_kernel_variants(D, variants):
         check(case, variant=v, num_splits=3)
 
 
+def test_workspace_survives_shape_changes():
+    """The split-merge arrival counters live in a shared, reused workspace: launches of different
+    (B, heads, splits) shapes must not see each other's leftovers (regression: counters used to sit
+    in front of partials whose layout moved with the shape)."""
+    shapes = [(3, 32, 8, 128, 7), (16, 8, 8, 128, 3), (2, 64, 8, 128, 16), (24, 28, 4, 128, 2), (5, 14, 2, 64, 9), (32, 32, 8, 128, 5)]
+    for rep in range(2):
+        for i, (B, Hq, Hkv, D, S) in enumerate(shapes):
+            lens = [(37 * (b + 1) * (i + 2)) % 900 for b in range(B)]
+            check(make_paged_case(B, Hq, Hkv, D, lens, seed=50 + i), num_splits=S)
+
+
 def test_head_groups_over_16():
     """G = 32 > 16 query heads per KV head: two head groups re-stream the KV head."""
     case = make_paged_case(3, 32, 1, 64, [300, 17, 1025], seed=4)
