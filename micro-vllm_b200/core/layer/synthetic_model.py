@@ -69,7 +69,7 @@ def _linear(i, o, bias, dtype, device, gen, std, fast=False):
 
 def build_synthetic_model(shape: Shape, n_layers: int | None = None, device="cuda", dtype=torch.bfloat16,
                           seed: int = 0, std: float = 0.02, vocab: int | None = None,
-                          norm_weight_jitter: float = 0.1, fast_init: bool = False):
+                          norm_weight_jitter: float = 0.1, fast_init: bool = False, peaky: bool = False):
     """Deterministic random-init tree; the same seed gives bit-identical weights on every rank
     (CPU generator by default; ``fast_init`` draws on the device for the big bench shapes)."""
     gen = (torch.Generator(device=device) if fast_init else torch.Generator()).manual_seed(seed)
@@ -106,4 +106,13 @@ def build_synthetic_model(shape: Shape, n_layers: int | None = None, device="cud
     tr.ln_f = RMSNormModule(H, shape.eps, dtype, device)
     model.transformer = tr
     model.lm_head = _linear(H, V, False, dtype, device, gen, std, fast_init)
+    if peaky:
+        # Separated logits for greedy-parity tests: tie the head to a PERMUTED embedding table,
+        # lm_head[pi(t)] = wte[t].  With small residual-branch weights the hidden state stays
+        # close to the input embedding, so the logit of pi(t) stands hundreds of units above the
+        # rest (like a trained model's peaked distribution) while the layers' context-dependent
+        # contribution still decides the winner whenever it is large enough.
+        pi = torch.randperm(V, generator=torch.Generator().manual_seed(seed + 1)).to(device)
+        with torch.no_grad():
+            model.lm_head.weight.index_copy_(0, pi, tr.wte.weight)
     return model

@@ -47,6 +47,15 @@ def test_chunked_prefill_on_cached_prefix(prefix, S):
     check_prefill(case)
 
 
+def test_prefill_long_prompt_many_tiles():
+    """16 KV tiles per query tile: exercises the K/V ring phases, S double buffering and the lazy
+    O rescale far beyond the first wrap-around."""
+    case = make_paged_case(1, 8, 2, 128, [0], S_new=2048, seed=21)
+    check_prefill(case)
+    case = make_paged_case(1, 4, 4, 64, [1100], S_new=1500, seed=22)
+    check_prefill(case)
+
+
 def test_prefill_interleaved_and_noncausal():
     case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=3)
     check_prefill(case, interleaved=True)
