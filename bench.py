@@ -233,24 +233,32 @@ def run_b200_arm(args):
         q = x[:, : Hq * D].view(B, Hq, D)
         k = x[:, Hq * D: (Hq + Hkv) * D].view(B, Hkv, D)
         v = x[:, (Hq + Hkv) * D:].view(B, Hkv, D)
+        # pdl: inside a decode step the kernel launched before a layer's attention never writes
+        # the lengths, the block table or that layer's cached pages (B200_DECODE_FLAG_PDL)
         b200ops.paged_attn_decode(q, mgr.k_caches[l], mgr.v_caches[l], k, v, cos, sin, seqlens, block_table,
                                   rotary_interleaved=False, out=out_dev[l], num_splits=num_splits,
-                                  variant=args.variant)
+                                  variant=args.variant, pdl=args.pdl)
 
-    def all_layers():
-        for l in range(L):
+    def layers(lo, hi):
+        for l in range(lo, hi):
             layer_call(l)
 
-    # warm-up on a side stream, then capture the 32 launches in one graph
-    s = torch.cuda.Stream()
-    s.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(s):
-        all_layers()
-    torch.cuda.current_stream().wait_stream(s)
-    torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        all_layers()
+    def capture(lo, hi):
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            layers(lo, hi)                       # warm-up on a side stream
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            layers(lo, hi)
+        return g
+
+    graph = capture(0, L)                        # the 32 launches of one decode step in one graph
+    n_chunks = 8                                 # e2e: host<->device copies pipelined against compute
+    bounds = [(c * L // n_chunks, (c + 1) * L // n_chunks) for c in range(n_chunks)]
+    chunk_graphs = [capture(lo, hi) for lo, hi in bounds]
 
     def sync_all():
         if world > 1:
@@ -281,13 +289,36 @@ def run_b200_arm(args):
     kernel_us = ms_step * 1e3 / L
     achieved = bytes_layer / (kernel_us * 1e-6) / 1e9
 
-    # ---- e2e: host buffers in, host buffers out, metadata rebuilt from Python lists every step
+    # ---- e2e: host buffers in, host buffers out, metadata rebuilt from Python lists every step.
+    # The layers are driven in 8 chunks so that the H2D copy of chunk c+1 and the D2H copy of
+    # chunk c-1 overlap the attention of chunk c (two copy streams + events); every byte still
+    # crosses PCIe inside the timed region.
+    main = torch.cuda.current_stream()
+    h2d_s, d2h_s = torch.cuda.Stream(), torch.cuda.Stream()
+    ev_in = [torch.cuda.Event() for _ in range(n_chunks)]
+    ev_out = [torch.cuda.Event() for _ in range(n_chunks)]
+    ev_step = torch.cuda.Event()
+    out_view = out_dev.view(L, B, Hq * D)
+
     def e2e_step():
         mgr.cache_batch_data(seq_ids, lens)
-        qkv_dev.copy_(qkv_host, non_blocking=True)
-        graph.replay()
-        out_host.copy_(out_dev.view(L, B, Hq * D), non_blocking=True)
+        h2d_s.wait_event(ev_step)                       # previous step's compute has consumed qkv_dev
+        with torch.cuda.stream(h2d_s):
+            for c, (lo, hi) in enumerate(bounds):
+                qkv_dev[lo:hi].copy_(qkv_host[lo:hi], non_blocking=True)
+                ev_in[c].record(h2d_s)
+        for c in range(n_chunks):
+            main.wait_event(ev_in[c])
+            chunk_graphs[c].replay()
+            ev_out[c].record(main)
+        ev_step.record(main)
+        with torch.cuda.stream(d2h_s):
+            for c, (lo, hi) in enumerate(bounds):
+                d2h_s.wait_event(ev_out[c])
+                out_host[lo:hi].copy_(out_view[lo:hi], non_blocking=True)
+        main.wait_stream(d2h_s)
 
+    ev_step.record(main)
     for _ in range(max(3, args.warmup)):
         e2e_step()
     sync_all()
@@ -329,7 +360,8 @@ def run_b200_arm(args):
                    "l2": "inputs (16 GiB KV per step) larger than L2; no flush needed",
                    "parallelism": f"kv-head shard per rank x{world}, no collective in attention",
                    "num_splits": num_splits or b200ops.decode_num_splits(B, Hkv, per_seq * page, b200ops.sm_count(dev)),
-                   "variant": args.variant},
+                   "variant": args.variant, "pdl": args.pdl,
+                   "e2e_pipeline": f"{n_chunks} chunks of {L // n_chunks} layers, H2D/D2H on side streams"},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": UNIT,
                      "frac": round(achieved / peak, 4), "traffic": traffic, "kernel": "paged_decode_kernel",
                      "kernel_us": round(kernel_us, 3), "algorithmic_bytes_per_launch": bytes_layer,
@@ -352,6 +384,7 @@ def main():
     ap.add_argument("--splits", type=int, default=0, help="override the split-KV count (0 = heuristic)")
     ap.add_argument("--variant", type=int, default=0, help="decode kernel tuning variant")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pdl", type=int, default=0, help="programmatic dependent launch: 0 off, 1 early trigger, 2 late trigger")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

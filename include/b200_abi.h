@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 3
+#define B200_ABI_VERSION 4
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -148,7 +148,18 @@ typedef struct b200_decode_args {
     int32_t num_splits;       /* >= 1; grid is (num_splits, Hkv*groups, B)        */
     int32_t variant;          /* tuning variant, 0 = default                      */
     float   softmax_scale;
+    int32_t flags;            /* B200_DECODE_FLAG_*                               */
 } b200_decode_args;
+
+/* Launch with programmatic stream serialization (PDL): the kernel may start, read
+ * cache_seqlens / block_table and prefetch cached K/V pages while the PRECEDING kernel in
+ * the stream is still draining; q, k_new, v_new, the workspace and all writes wait for it.
+ * Only set it when the preceding kernel does not produce cache_seqlens, block_table or
+ * cache pages this call reads (true inside the decode layer loop: the predecessor is the
+ * QKV projection, model_graph.py:141-148). */
+#define B200_DECODE_FLAG_PDL 1
+/* with PDL: release the dependent kernel after the streaming loop instead of at kernel start */
+#define B200_DECODE_FLAG_PDL_LATE 2
 
 int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
                                     int32_t num_splits);

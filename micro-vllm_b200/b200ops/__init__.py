@@ -151,9 +151,13 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
                       cache_seqlens: torch.Tensor, block_table: torch.Tensor,
                       softmax_scale: Optional[float] = None, rotary_interleaved: bool = False,
                       num_splits: int = 0, out: Optional[torch.Tensor] = None,
-                      softmax_lse: Optional[torch.Tensor] = None, variant: int = 0) -> torch.Tensor:
+                      softmax_lse: Optional[torch.Tensor] = None, variant: int = 0,
+                      pdl: int = 0) -> torch.Tensor:
     """q [B, Hq, D]; k_new/v_new [B, Hkv, D]; caches [n_blocks, block_size, Hkv, D];
-    returns out [B, Hq, D] (allocated unless given)."""
+    returns out [B, Hq, D] (allocated unless given).  ``pdl`` = 1 / 2 launches with programmatic
+    stream serialization, releasing the next kernel at start / after the streaming loop (see
+    B200_DECODE_FLAG_PDL in b200_abi.h for the precondition; measured slower than a plain launch on
+    back-to-back decode kernels, so it is off by default)."""
     _req_cuda(q, k_cache, v_cache, k_new, v_new, rotary_cos, rotary_sin, cache_seqlens, block_table)
     B, Hq, D = q.shape
     n_blocks, block_size, Hkv, Dc = k_cache.shape
@@ -197,6 +201,7 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     if num_splits <= 0:
         num_splits = decode_num_splits(B, Hkv, block_table.shape[1] * block_size, sm_count(q.device))
     a.num_splits, a.variant = int(num_splits), int(variant)
+    a.flags = 0 if not pdl else (_lib.DECODE_FLAG_PDL | (_lib.DECODE_FLAG_PDL_LATE if int(pdl) == 2 else 0))
     a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 1.0 / math.sqrt(D)
     if num_splits > 1:
         need = lib.b200_decode_workspace_bytes(B, Hq, Hkv, D, num_splits)

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class DecodeArgs(C.Structure):
@@ -34,8 +34,12 @@ class DecodeArgs(C.Structure):
         ("kc_stride_blk", _i64), ("kc_stride_tok", _i64), ("kc_stride_h", _i64),
         ("vc_stride_blk", _i64), ("vc_stride_tok", _i64), ("vc_stride_h", _i64),
         ("bt_stride_b", _i64),
-        ("num_splits", _i32), ("variant", _i32), ("softmax_scale", _f32),
+        ("num_splits", _i32), ("variant", _i32), ("softmax_scale", _f32), ("flags", _i32),
     ]
+
+
+DECODE_FLAG_PDL = 1
+DECODE_FLAG_PDL_LATE = 2
 
 
 class PrefillArgs(C.Structure):

@@ -59,6 +59,10 @@ class ModelGraphRunner:
         self.dtype = dtype
         self.top_k = top_k
 
+        # The kernel launched right before a layer's attention is its QKV projection, which never
+        # writes the lengths, the block table or cached pages, so programmatic dependent launch
+        # would be legal here; measured on B200 it does not pay (profiles/r01), so it stays off.
+        self.use_pdl = 0
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
         self.rope = RoPE()
@@ -134,7 +138,7 @@ class ModelGraphRunner:
         b200ops.paged_attn_decode(q, k_cache, v_cache, k, v,
                                   self.attention._cos_pool, self.attention._sin_pool,
                                   cache_lens, block_table, softmax_scale=self.attention.scale,
-                                  rotary_interleaved=False, out=attn)
+                                  rotary_interleaved=False, out=attn, pdl=self.use_pdl)
         out = self._attn_out[:bs]
         torch.matmul(self._attn[:bs], block.attn._o, out=out)
         return out

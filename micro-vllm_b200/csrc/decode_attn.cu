@@ -57,6 +57,8 @@ struct DecodeParams {
     int B, Hq, Hkv, G, ngroups, gpg;
     int rotary_dim, interleaved, rot_rows;
     int n_blocks, block_size, max_blocks_per_seq;
+    int page_shift;                      // log2(block_size) or -1 when block_size is not a power of two
+    int pdl;                             // launched with programmatic stream serialization
     int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, o_sb, o_sh;
     int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
     float scale, scale_log2;
@@ -130,7 +132,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
         if (i < n_iters) {
             const int t0 = (c0 + i) * C::CH + warp * TPS;
             if (t0 < seqlen_k) {
-                const int pe = t0 / p.block_size;
+                const int pe = p.page_shift >= 0 ? (t0 >> p.page_shift) : (t0 / p.block_size);
                 int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : -1;
                 const bool ok = (page >= 0) && (page < p.n_blocks);
                 if (!ok) page = 0;
@@ -162,6 +164,14 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     // cache_seqlens and the block table.
 #pragma unroll
     for (int i = 0; i < STAGES - 1; ++i) issue(i);
+
+    // Programmatic dependent launch: everything above only read state that the caller
+    // guarantees is older than the preceding kernel in the stream (lengths, block table, cached
+    // pages); q / k_new / v_new, the workspace and every global write come after the wait.
+    if (p.pdl) {
+        if (p.pdl == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
 
     // ---- prologue under the in-flight copies: rotate q (and k_new), stage v_new
     const int rd = (p.cos != nullptr && has_new) ? p.rotary_dim : 0;
@@ -198,7 +208,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
 
     // ---- append: rotated k_new / raw v_new -> page block_table[b, pos / bs], slot pos % bs
     if (owns_new && grp == 0 && tid < 2 * CPR) {
-        const int pe = pos / p.block_size;
+        const int pe = p.page_shift >= 0 ? (pos >> p.page_shift) : (pos / p.block_size);
         const int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : -1;
         if (page >= 0 && page < p.n_blocks) {
             const int slot = pos - pe * p.block_size;
@@ -334,6 +344,9 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
         l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     }
     cp_async_wait<0>();
+    // late trigger: the next kernel's CTAs may take over SMs from here on (their KV prefetch
+    // overlaps this kernel's merge epilogue and tail)
+    if (p.pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();                                    // ring buffers are dead -> reuse as merge scratch
 
     // ---- merge the warps of this CTA
@@ -493,7 +506,18 @@ static int launch_decode(const DecodeParams& p, int S, cudaStream_t st) {
         attr_done = true; attr_dev = dev;
     }
     dim3 grid((unsigned)S, (unsigned)(p.Hkv * p.ngroups), (unsigned)p.B);
-    paged_decode_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(p);
+    if (p.pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid; cfg.blockDim = dim3(C::THREADS); cfg.dynamicSmemBytes = C::SMEM; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, paged_decode_kernel<C>, p);
+        if (e != cudaSuccess) { set_error("decode: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+    } else {
+        paged_decode_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(p);
+    }
     B200_CHECK_LAUNCH();
     return 0;
 }
@@ -559,6 +583,9 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     p.B = a->B; p.Hq = a->Hq; p.Hkv = a->Hkv; p.G = G; p.ngroups = ngroups; p.gpg = (G + ngroups - 1) / ngroups;
     p.rotary_dim = rot ? a->rotary_dim : 0; p.interleaved = a->rotary_interleaved; p.rot_rows = rot ? a->rot_rows : 1;
     p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq;
+    p.page_shift = -1;
+    for (int sft = 5; sft < 31; ++sft) if ((1 << sft) == a->block_size) p.page_shift = sft;
+    p.pdl = (a->flags & B200_DECODE_FLAG_PDL) ? ((a->flags & B200_DECODE_FLAG_PDL_LATE) ? 2 : 1) : 0;
     p.q_sb = a->q_stride_b; p.q_sh = a->q_stride_h; p.k_sb = a->k_stride_b; p.k_sh = a->k_stride_h;
     p.v_sb = a->v_stride_b; p.v_sh = a->v_stride_h; p.o_sb = a->o_stride_b; p.o_sh = a->o_stride_h;
     p.kc_sblk = a->kc_stride_blk; p.kc_stok = a->kc_stride_tok; p.kc_sh = a->kc_stride_h;
@@ -579,6 +606,9 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
             case 6: return launch_decode<DCfg<128, 4, 16, 2, 3>>(p, S, st);   //  64 KB, 3 CTA/SM (default: best on the B200 sweep)
             case 7: return launch_decode<DCfg<128, 8, 16, 2, 1>>(p, S, st);   // 128 KB
             case 8: return launch_decode<DCfg<128, 2, 32, 3, 2>>(p, S, st);   //  96 KB, 2 CTA/SM
+            case 9: return launch_decode<DCfg<128, 2, 32, 2, 3>>(p, S, st);   //  64 KB, 3 CTA/SM
+            case 10: return launch_decode<DCfg<128, 4, 32, 2, 1>>(p, S, st);  // 128 KB
+            case 11: return launch_decode<DCfg<128, 2, 16, 3, 4>>(p, S, st);  //  48 KB, 4 CTA/SM
             default: B200_FAIL(B200_E_RANGE, "decode: unknown variant %d", a->variant);
         }
     } else {

@@ -21,31 +21,30 @@ void set_error(const char* fmt, ...) {
 }
 
 // ============================================================== SwiGLU
-// One thread = UNROLL independent 16-byte (8 x bf16) output vectors; all loads
-// of a thread are issued before the first use (2*UNROLL 128-bit loads in flight).
-template <int UNROLL>
+// grid = (column chunks, rows): no integer division on the hot path.  One thread owns VPT
+// 16-byte (8 x bf16) output vectors of one row, strided by the block so that every warp access
+// is a contiguous 512 B; all 2*VPT loads are issued before the first use.
+template <int VPT>
 __global__ void __launch_bounds__(256)
 swiglu_vec_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ out,
-                  int64_t rows, int64_t dv /* d/8 */, int64_t stride_in, int64_t stride_out) {
-    const int64_t total = rows * dv;
-    const int64_t base = (int64_t)blockIdx.x * (UNROLL * 256) + threadIdx.x;
-    uint4 up[UNROLL], gate[UNROLL];
-    int64_t orow[UNROLL], ocol[UNROLL];
+                  int dv /* d/8 */, int64_t stride_in, int64_t stride_out) {
+    const int64_t row = blockIdx.y;
+    const int c0 = blockIdx.x * (VPT * 256) + threadIdx.x;
+    const __nv_bfloat16* up_p = gu + row * stride_in;
+    const __nv_bfloat16* gate_p = up_p + (int64_t)dv * 8;
+    uint4 up[VPT], gate[VPT];
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-        const int64_t idx = base + (int64_t)u * 256;
-        if (idx < total) {
-            const int64_t r = idx / dv, c = idx - r * dv;
-            orow[u] = r; ocol[u] = c;
-            const __nv_bfloat16* p = gu + r * stride_in + c * 8;
-            up[u] = ld_nc_v4(p);
-            gate[u] = ld_nc_v4(p + dv * 8);
+    for (int u = 0; u < VPT; ++u) {
+        const int c = c0 + u * 256;
+        if (c < dv) {
+            up[u] = ld_nc_v4(up_p + (int64_t)c * 8);
+            gate[u] = ld_nc_v4(gate_p + (int64_t)c * 8);
         }
     }
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-        const int64_t idx = base + (int64_t)u * 256;
-        if (idx < total) {
+    for (int u = 0; u < VPT; ++u) {
+        const int c = c0 + u * 256;
+        if (c < dv) {
             const uint32_t* pu = &up[u].x;
             const uint32_t* pg = &gate[u].x;
             uint4 o;
@@ -55,11 +54,11 @@ swiglu_vec_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restric
                 const float g0 = bf16lo(pg[i]), g1 = bf16hi(pg[i]);
                 const float u0 = bf16lo(pu[i]), u1 = bf16hi(pu[i]);
                 // silu(g) = g * sigmoid(g) = g / (1 + exp(-g))   (swiglu.py:40-42)
-                const float s0 = g0 * (1.0f / (1.0f + __expf(-g0)));
-                const float s1 = g1 * (1.0f / (1.0f + __expf(-g1)));
+                const float s0 = __fdividef(g0, 1.0f + __expf(-g0));
+                const float s1 = __fdividef(g1, 1.0f + __expf(-g1));
                 po[i] = pack_bf16(s0 * u0, s1 * u1);
             }
-            st_na_v4(out + orow[u] * stride_out + ocol[u] * 8, o);
+            st_na_v4(out + row * stride_out + (int64_t)c * 8, o);
         }
     }
 }
@@ -318,11 +317,22 @@ extern "C" int b200_swiglu(const void* gate_up, void* out, int64_t rows, int64_t
     cudaStream_t st = (cudaStream_t)stream;
     auto G = (const __nv_bfloat16*)gate_up; auto O = (__nv_bfloat16*)out;
     const bool vec = (d % 8 == 0) && (stride_in % 8 == 0) && (stride_out % 8 == 0) && aligned16(gate_up) && aligned16(out);
-    if (vec) {
-        const int64_t total = rows * (d / 8);
-        constexpr int UNROLL = 4;
-        const int64_t blocks = (total + UNROLL * 256 - 1) / (UNROLL * 256);
-        swiglu_vec_kernel<UNROLL><<<(unsigned)blocks, 256, 0, st>>>(G, O, rows, d / 8, stride_in, stride_out);
+    if (vec && rows <= 65535 * 32768LL && d / 8 < (1 << 30)) {
+        const int dv = (int)(d / 8);
+        // rows go to grid.y (<= 65535 per launch); few rows (decode) -> 1 vector per thread so the
+        // whole chip is used, many rows (prefill) -> 4 vectors per thread for bytes in flight
+        for (int64_t r0 = 0; r0 < rows; r0 += 65535) {
+            const unsigned nr = (unsigned)((rows - r0 < 65535) ? rows - r0 : 65535);
+            const __nv_bfloat16* g = G + r0 * stride_in;
+            __nv_bfloat16* o = O + r0 * stride_out;
+            if (rows >= 256 && dv >= 1024) {
+                swiglu_vec_kernel<4><<<dim3((dv + 1023) / 1024, nr), 256, 0, st>>>(g, o, dv, stride_in, stride_out);
+            } else if (rows >= 256 && dv >= 512) {
+                swiglu_vec_kernel<2><<<dim3((dv + 511) / 512, nr), 256, 0, st>>>(g, o, dv, stride_in, stride_out);
+            } else {
+                swiglu_vec_kernel<1><<<dim3((dv + 255) / 256, nr), 256, 0, st>>>(g, o, dv, stride_in, stride_out);
+            }
+        }
     } else {
         int64_t blocks = (rows * d + 255) / 256;
         if (blocks > 148 * 32) blocks = 148 * 32;

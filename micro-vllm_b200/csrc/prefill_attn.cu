@@ -12,10 +12,10 @@
 //      128B-swizzled so the tiles are UMMA-canonical).  One thread issues
 //      tcgen05.mma: S = Q.K^T into a double-buffered TMEM accumulator and
 //      O += P.V into a second TMEM accumulator (V is consumed MN-major, no
-//      transpose).  Four softmax warps own one query row per thread (TMEM lane =
-//      row): tcgen05.ld the scores, online softmax in fp32 with lazy rescaling,
-//      write P as a K-major bf16 operand to shared memory, rescale O in TMEM only
-//      when the running max moved by more than 2^8.            (tensor-core bound)
+//      transpose).  Eight softmax warps put two threads on every query row (TMEM lane =
+//      row, 64 key columns each): tcgen05.ld the scores, online softmax in fp32 with
+//      lazy rescaling, write P as a K-major bf16 operand to shared memory, rescale O in
+//      TMEM only when the running max moved by more than 2^8.   (tensor-core bound)
 #include "common.cuh"
 #include <cuda.h>
 #include <math_constants.h>
@@ -89,6 +89,22 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
                     "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
                     "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
                  : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 :: "r"(taddr),
+                    "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                    "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+                 : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (128 rows = 128 lanes, 16-bit elements packed two
+// per 32-bit column, 8 columns per K=16 step) is read from tensor memory, not shared memory
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -185,8 +201,10 @@ struct PCfg {
     static constexpr int OFF_P = OFF_V + KV_STAGES * TILE_B;
     static constexpr int OFF_BAR = OFF_P + P_B;
     static constexpr int NBARS = 16;
-    static constexpr int SMEM = OFF_BAR + NBARS * 8 + 16 + 1024;   // +1024: manual 1 KB alignment
-    static constexpr int THREADS = 192;                       // warp0 TMA, warp1 MMA, warps2-5 softmax
+    static constexpr int OFF_XCH = OFF_BAR + NBARS * 8 + 16;   // softmax row max / row sum exchange [2][2][128] f32
+    static constexpr int SMEM = OFF_XCH + 2 * 2 * 128 * 4 + 1024;   // +1024: manual 1 KB alignment
+    static constexpr int SOFTMAX_THREADS = 256;
+    static constexpr int THREADS = 64 + SOFTMAX_THREADS;      // warp0 TMA, warp1 MMA, warps 2-9 softmax
     static constexpr int TMEM_COLS = 512;
     static constexpr int TM_S0 = 0, TM_S1 = 128, TM_O = 256;
 };
@@ -222,9 +240,9 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         for (int s = 0; s < 2; ++s) {
             mbar_init(bar(BAR_KF + s), 1); mbar_init(bar(BAR_KE + s), 1);
             mbar_init(bar(BAR_VF + s), 1); mbar_init(bar(BAR_VE + s), 1);
-            mbar_init(bar(BAR_SF + s), 1); mbar_init(bar(BAR_SE + s), 128);
+            mbar_init(bar(BAR_SF + s), 1); mbar_init(bar(BAR_SE + s), C::SOFTMAX_THREADS);
         }
-        mbar_init(bar(BAR_PF), 128); mbar_init(bar(BAR_PE), 1);
+        mbar_init(bar(BAR_PF), C::SOFTMAX_THREADS); mbar_init(bar(BAR_PE), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
     }
@@ -307,27 +325,33 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
             issue_pv(n_tiles - 1);
         }
     } else {
-        // ===================================================== softmax / correction / epilogue (4 warps, 1 row per thread)
+        // ===================================================== softmax / correction / epilogue
+        // 8 warps: TWO threads per query row (TMEM lane = row; warps w and w+4 share a lane quarter),
+        // each owning 64 of the 128 key columns of a tile and half of the O columns.
         const int quarter = warp & 3;                          // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;                      // which 64 key columns / which half of D
         const int row = quarter * 32 + lane;
         const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
         const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
         const float sl2 = p.scale_log2;
+        constexpr int HC = C::BN / 2;                          // key columns per thread
+        constexpr int HD = D / 2;                              // O columns per thread
         float m_ref = -CUDART_INF_F, l = 0.0f;
-        const uint32_t p_row = sP + (uint32_t)row * 128u;
+        const uint32_t p_row = sP + (uint32_t)half * C::SLAB_B + (uint32_t)row * 128u;
         const int sw = row & 7;
+        volatile float* xch = reinterpret_cast<volatile float*>(smem + C::OFF_XCH);   // [2 parity][2 halves][128 rows]
 
         for (int j = 0; j < n_tiles; ++j) {
             const int st = j & 1;
-            const int n0 = j * C::BN;
+            const int n0 = j * C::BN + half * HC;
             mbar_wait(bar(BAR_SF + st), (uint32_t)(j >> 1) & 1u);
             tc_fence_after();
-            uint32_t su[C::BN];                                // scores, fp32 bit patterns (TMEM registers)
+            uint32_t su[HC];                                   // scores, fp32 bit patterns (TMEM registers)
 #define SF(c) __uint_as_float(su[(c)])
             {
-                const uint32_t ts = tmem + lane_sel + (st ? C::TM_S1 : C::TM_S0);
+                const uint32_t ts = tmem + lane_sel + (st ? C::TM_S1 : C::TM_S0) + half * HC;
 #pragma unroll
-                for (int c = 0; c < C::BN / 32; ++c) {
+                for (int c = 0; c < HC / 32; ++c) {
                     uint32_t r[32];
                     tmem_ld32(ts + c * 32, r);
 #pragma unroll
@@ -338,17 +362,22 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
             tc_fence_before();
             mbar_arrive(bar(BAR_SE + st));                     // S buffer may be overwritten by QK_{j+2}
 
-            if (n0 + C::BN - 1 > prefix + q0 || n0 + C::BN > seqlen_k) {   // diagonal or tail tile
+            if (n0 + HC - 1 > prefix + q0 || n0 + HC > seqlen_k) {   // diagonal or tail columns
 #pragma unroll
-                for (int c = 0; c < C::BN; ++c) {
+                for (int c = 0; c < HC; ++c) {
                     const int tok = n0 + c;
                     if (tok > qpos || tok >= seqlen_k) su[c] = 0xff800000u;   // -inf
                 }
             }
             float mx = SF(0);
 #pragma unroll
-            for (int c = 1; c < C::BN; ++c) mx = fmaxf(mx, SF(c));
+            for (int c = 1; c < HC; ++c) mx = fmaxf(mx, SF(c));
+            // row max across the two column halves (parity-double-buffered exchange)
+            xch[(j & 1) * 256 + half * 128 + row] = mx;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mx = fmaxf(mx, xch[(j & 1) * 256 + (half ^ 1) * 128 + row]);
             // lazy rescale: keep the old reference max unless it is off by more than 2^8
+            // (both threads of a row take the same decision from the same numbers)
             float alpha = 1.0f;
             bool grow = false;
             if (j == 0) {
@@ -362,25 +391,25 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
             const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
             float rs = 0.0f;
 #pragma unroll
-            for (int c = 0; c < C::BN; ++c) { const float e = fast_exp2(SF(c) * sl2 - mr); su[c] = __float_as_uint(e); rs += e; }
+            for (int c = 0; c < HC; ++c) { const float e = fast_exp2(SF(c) * sl2 - mr); su[c] = __float_as_uint(e); rs += e; }
             l += rs;
 
             mbar_wait(bar(BAR_PE), ((uint32_t)j & 1u) ^ 1u);   // PV_{j-1} retired: P buffer free, O stable
             tc_fence_after();
 #pragma unroll
-            for (int c = 0; c < C::BN / 8; ++c) {              // 16-byte chunks of 8 tokens, K-major SW128
+            for (int c = 0; c < HC / 8; ++c) {                 // 16-byte chunks of 8 tokens, K-major SW128 slab `half`
                 uint4 v;
                 v.x = pack_bf16(SF(c * 8 + 0), SF(c * 8 + 1));
                 v.y = pack_bf16(SF(c * 8 + 2), SF(c * 8 + 3));
                 v.z = pack_bf16(SF(c * 8 + 4), SF(c * 8 + 5));
                 v.w = pack_bf16(SF(c * 8 + 6), SF(c * 8 + 7));
-                const uint32_t addr = p_row + (uint32_t)(c >> 3) * C::SLAB_B + (uint32_t)(((c & 7) ^ sw) << 4);
+                const uint32_t addr = p_row + (uint32_t)((c ^ sw) << 4);
                 asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
             }
             if (j > 0 && __any_sync(0xffffffffu, grow)) {      // warp-uniform: tcgen05.ld/st are warp-collective
-                const uint32_t to = tmem + lane_sel + C::TM_O;
+                const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
 #pragma unroll
-                for (int c = 0; c < D / 32; ++c) {
+                for (int c = 0; c < HD / 32; ++c) {
                     uint32_t r[32];
                     tmem_ld32(to + c * 32, r);
                     tmem_wait_ld();
@@ -396,15 +425,304 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
 #undef SF
         }
 
-        // epilogue: O / l -> bf16 -> global
+        // epilogue: row sum across the two halves, O / l -> bf16 -> global (each thread half of D)
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        xch[half * 128 + row] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        l += xch[(half ^ 1) * 128 + row];
         mbar_wait(bar(BAR_PE), (uint32_t)(n_tiles - 1) & 1u);
         tc_fence_after();
         const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
         const bool live = (q0 + row) < p.S;
-        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh;
-        const uint32_t to = tmem + lane_sel + C::TM_O;
+        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh + half * HD;
+        const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
+        for (int c = 0; c < HD / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(to + c * 32, r);
+            tmem_wait_ld();
+            if (live) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 v;
+                    v.x = pack_bf16(__uint_as_float(r[i * 8 + 0]) * inv, __uint_as_float(r[i * 8 + 1]) * inv);
+                    v.y = pack_bf16(__uint_as_float(r[i * 8 + 2]) * inv, __uint_as_float(r[i * 8 + 3]) * inv);
+                    v.z = pack_bf16(__uint_as_float(r[i * 8 + 4]) * inv, __uint_as_float(r[i * 8 + 5]) * inv);
+                    v.w = pack_bf16(__uint_as_float(r[i * 8 + 6]) * inv, __uint_as_float(r[i * 8 + 7]) * inv);
+                    *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ kernel 2b: attention, operands in TMEM
+// Same pipeline as prefill_attn_kernel, but the two A operands never touch shared memory: the
+// rotated Q tile is written ONCE into tensor memory (tcgen05.st by the softmax warps) and the
+// probabilities P go registers -> TMEM as packed bf16x2.  With Q and P in shared memory every KV
+// tile moves 224 KB through the 128 B/clk shared-memory port (MMA operand reads 128 KB, P 32 KB,
+// TMA fill 64 KB) against 1024 tensor-pipe cycles -> shared-memory bound at ~55 %; with both in
+// TMEM only the K and V tiles remain (128 KB per tile) and the freed 64 KB buy a third K/V stage.
+template <int D_>
+struct PCfg2 {
+    static constexpr int D = D_;
+    static constexpr int BM = 128, BN = 128;
+    static constexpr int SLAB_B = 128 * 128;
+    static constexpr int DSLABS = D / 64;
+    static constexpr int TILE_B = DSLABS * SLAB_B;
+    static constexpr int KV_STAGES = 3;
+    static constexpr int OFF_K = 0;
+    static constexpr int OFF_V = OFF_K + KV_STAGES * TILE_B;
+    static constexpr int OFF_BAR = OFF_V + KV_STAGES * TILE_B;
+    static constexpr int NBARS = 20;
+    static constexpr int OFF_XCH = OFF_BAR + NBARS * 8 + 16;
+    static constexpr int SMEM = OFF_XCH + 2 * 2 * 128 * 4 + 1024;
+    static constexpr int SOFTMAX_THREADS = 256;
+    static constexpr int THREADS = 64 + SOFTMAX_THREADS;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int TM_S0 = 0, TM_S1 = 128, TM_O = 256, TM_Q = 384, TM_P = 448;   // Q: D/2 columns, P: 64 columns
+};
+
+enum { B2_Q = 0, B2_KF = 1, B2_KE = 4, B2_VF = 7, B2_VE = 10, B2_SF = 13, B2_SE = 15, B2_PF = 17, B2_PE = 18 };
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                         const __nv_bfloat16* __restrict__ q_rot, const __grid_constant__ PrefillParams p) {
+    constexpr int D = C::D;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_u32 = smem_u32(smem_raw);
+    const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw_u32);
+    const uint32_t sK = base + C::OFF_K, sV = base + C::OFF_V;
+    const uint32_t bars = base + C::OFF_BAR;
+    auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
+    volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qt = (int)gridDim.x - 1 - (int)blockIdx.x;
+    const int q0 = qt * C::BM;
+    const int hq = blockIdx.y, b = blockIdx.z;
+    const int kvh = hq / p.G;
+    const int prefix = __ldg(p.seqlens + b);
+    const int seqlen_k = prefix + p.S;
+    const int kv_end = p.causal ? min(seqlen_k, prefix + q0 + C::BM) : seqlen_k;
+    const int n_tiles = (kv_end + C::BN - 1) / C::BN;
+
+    if (tid == 0) {
+        mbar_init(bar(B2_Q), C::SOFTMAX_THREADS);
+        for (int s = 0; s < C::KV_STAGES; ++s) {
+            mbar_init(bar(B2_KF + s), 1); mbar_init(bar(B2_KE + s), 1);
+            mbar_init(bar(B2_VF + s), 1); mbar_init(bar(B2_VE + s), 1);
+        }
+        for (int s = 0; s < 2; ++s) { mbar_init(bar(B2_SF + s), 1); mbar_init(bar(B2_SE + s), C::SOFTMAX_THREADS); }
+        mbar_init(bar(B2_PF), C::SOFTMAX_THREADS); mbar_init(bar(B2_PE), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32((const void*)s_tmem)), "r"((uint32_t)C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer (K/V ring, 3 stages)
+        if (lane == 0) {
+            const int32_t* bt = p.block_table + (int64_t)b * p.bt_sb;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % C::KV_STAGES;
+                const uint32_t ph = (uint32_t)(j / C::KV_STAGES) & 1u;
+                const int n0 = j * C::BN;
+                const int pe = n0 / p.block_size;
+                int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : 0;
+                if (page < 0 || page >= p.n_blocks) page = 0;
+                const int tok = n0 - pe * p.block_size;
+                mbar_wait(bar(B2_KE + st), ph ^ 1u);
+                mbar_expect_tx(bar(B2_KF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(B2_KF + st), sl * 64, kvh, tok, page);
+                mbar_wait(bar(B2_VE + st), ph ^ 1u);
+                mbar_expect_tx(bar(B2_VF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sV + st * C::TILE_B + sl * C::SLAB_B, &tm_v, bar(B2_VF + st), sl * 64, kvh, tok, page);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer (one thread)
+        if (lane == 0) {
+            constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q (TMEM), B=K K-major
+            constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P (TMEM), B=V MN-major
+            auto issue_pv = [&](int t) {
+                const int st = t % C::KV_STAGES;
+                mbar_wait(bar(B2_VF + st), (uint32_t)(t / C::KV_STAGES) & 1u);
+                mbar_wait(bar(B2_PF), (uint32_t)t & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < C::BN / 16; ++k) {
+                    const uint64_t db = umma_desc_sw128(sV + st * C::TILE_B + k * 2048, C::SLAB_B, 1024);
+                    umma_bf16_ts(tmem + C::TM_O, tmem + C::TM_P + k * 8, db, IDESC_PV, (t > 0 || k > 0) ? 1u : 0u);
+                }
+                tc_commit(bar(B2_VE + st));
+                tc_commit(bar(B2_PE));
+            };
+            mbar_wait(bar(B2_Q), 0);
+            tc_fence_after();
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % C::KV_STAGES;
+                const int sb = j & 1;
+                mbar_wait(bar(B2_KF + st), (uint32_t)(j / C::KV_STAGES) & 1u);
+                mbar_wait(bar(B2_SE + sb), ((uint32_t)(j >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t db = umma_desc_sw128(sK + st * C::TILE_B + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    umma_bf16_ts(tmem + (sb ? C::TM_S1 : C::TM_S0), tmem + C::TM_Q + k * 8, db, IDESC_QK, k > 0 ? 1u : 0u);
+                }
+                tc_commit(bar(B2_KE + st));
+                tc_commit(bar(B2_SF + sb));
+                if (j > 0) issue_pv(j - 1);
+            }
+            issue_pv(n_tiles - 1);
+        }
+    } else {
+        // ===================================================== softmax / correction / epilogue (8 warps)
+        const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
+        const float sl2 = p.scale_log2;
+        constexpr int HC = C::BN / 2;
+        constexpr int HD = D / 2;
+        const bool live = (q0 + row) < p.S;
+
+        // ---- Q tile -> tensor memory, once: thread (row, half) stores D/2 bf16 = D/4 packed columns
+        {
+            constexpr int QW = HD / 2;                         // 32-bit words per thread: 32 (D=128) or 16 (D=64)
+            uint32_t qw[QW];
+            if (live) {
+                const __nv_bfloat16* src = q_rot + (((int64_t)b * p.S + (q0 + row)) * p.Hq + hq) * D + half * HD;
+#pragma unroll
+                for (int i = 0; i < QW / 4; ++i) {
+                    const uint4 v = ld_nc_v4(src + i * 8);
+                    qw[4 * i] = v.x; qw[4 * i + 1] = v.y; qw[4 * i + 2] = v.z; qw[4 * i + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < QW; ++i) qw[i] = 0u;
+            }
+            const uint32_t tq = tmem + lane_sel + C::TM_Q + half * QW;
+            if constexpr (QW == 32) tmem_st32(tq, *reinterpret_cast<const uint32_t(*)[32]>(qw));
+            else                    tmem_st16(tq, *reinterpret_cast<const uint32_t(*)[16]>(qw));
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar(B2_Q));
+        }
+
+        float m_ref = -CUDART_INF_F, l = 0.0f;
+        volatile float* xch = reinterpret_cast<volatile float*>(smem + C::OFF_XCH);
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int sb = j & 1;
+            const int n0 = j * C::BN + half * HC;
+            mbar_wait(bar(B2_SF + sb), (uint32_t)(j >> 1) & 1u);
+            tc_fence_after();
+            uint32_t su[HC];
+#define SF(c) __uint_as_float(su[(c)])
+            {
+                const uint32_t ts = tmem + lane_sel + (sb ? C::TM_S1 : C::TM_S0) + half * HC;
+#pragma unroll
+                for (int c = 0; c < HC / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(ts + c * 32, r);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) su[c * 32 + i] = r[i];
+                }
+                tmem_wait_ld();
+            }
+            tc_fence_before();
+            mbar_arrive(bar(B2_SE + sb));
+
+            if (n0 + HC - 1 > prefix + q0 || n0 + HC > seqlen_k) {
+#pragma unroll
+                for (int c = 0; c < HC; ++c) {
+                    const int tok = n0 + c;
+                    if (tok > qpos || tok >= seqlen_k) su[c] = 0xff800000u;
+                }
+            }
+            float mx = SF(0);
+#pragma unroll
+            for (int c = 1; c < HC; ++c) mx = fmaxf(mx, SF(c));
+            xch[(j & 1) * 256 + half * 128 + row] = mx;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mx = fmaxf(mx, xch[(j & 1) * 256 + (half ^ 1) * 128 + row]);
+            float alpha = 1.0f;
+            bool grow = false;
+            if (j == 0) {
+                m_ref = mx;
+            } else if ((mx - m_ref) * sl2 > 8.0f) {
+                alpha = fast_exp2((m_ref - mx) * sl2);
+                m_ref = mx;
+                l *= alpha;
+                grow = true;
+            }
+            const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
+            float rs = 0.0f;
+            uint32_t pw[HC / 2];                               // probabilities, packed bf16x2 (A operand of P.V)
+#pragma unroll
+            for (int c = 0; c < HC; c += 2) {
+                const float e0 = fast_exp2(SF(c) * sl2 - mr), e1 = fast_exp2(SF(c + 1) * sl2 - mr);
+                rs += e0 + e1;
+                pw[c >> 1] = pack_bf16(e0, e1);
+            }
+            l += rs;
+
+            mbar_wait(bar(B2_PE), ((uint32_t)j & 1u) ^ 1u);    // PV_{j-1} retired: P columns free, O stable
+            tc_fence_after();
+            tmem_st32(tmem + lane_sel + C::TM_P + half * (HC / 2), pw);
+            if (j > 0 && __any_sync(0xffffffffu, grow)) {
+                const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
+#pragma unroll
+                for (int c = 0; c < HD / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(to + c * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                    tmem_st32(to + c * 32, r);
+                }
+            }
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar(B2_PF));
+#undef SF
+        }
+
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        xch[half * 128 + row] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        l += xch[(half ^ 1) * 128 + row];
+        mbar_wait(bar(B2_PE), (uint32_t)(n_tiles - 1) & 1u);
+        tc_fence_after();
+        const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
+        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh + half * HD;
+        const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
+#pragma unroll
+        for (int c = 0; c < HD / 32; ++c) {
             uint32_t r[32];
             tmem_ld32(to + c * 32, r);
             tmem_wait_ld();
@@ -480,6 +798,23 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tk, const CU
     return 0;
 }
 
+template <class C>
+static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q_rot,
+                               const PrefillParams& p, cudaStream_t st) {
+    static int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_tmem_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
+        attr_dev = dev;
+    }
+    dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
+    prefill_attn_tmem_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, p);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -547,6 +882,11 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq; p.causal = a->causal;
     p.o_sb = a->o_stride_b; p.o_ss = a->o_stride_s; p.o_sh = a->o_stride_h; p.bt_sb = a->bt_stride_b;
     p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
-    if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
-    return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
+    if (a->variant == 1) {                      // operands staged in shared memory (first version, kept for A/B runs)
+        if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
+        return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
+    }
+    if (a->variant != 0) B200_FAIL(B200_E_RANGE, "prefill: unknown variant %d", a->variant);
+    if (a->D == 128) return launch_prefill_tmem<PCfg2<128>>(tk, tv, (const __nv_bfloat16*)a->workspace, p, st);
+    return launch_prefill_tmem<PCfg2<64>>(tk, tv, (const __nv_bfloat16*)a->workspace, p, st);
 }

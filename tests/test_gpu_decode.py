@@ -320,3 +320,46 @@ def test_cuda_graph_capture_and_replay():
                                    case_a["seqlens"] + 1, case_a["table"], case_a["scale"], True, False)
     assert_close(out, want2[:, 0])
     assert torch.equal(d["v_cache"].cpu(), vc_ref)
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_programmatic_dependent_launch_chain(mode):
+    """B200_DECODE_FLAG_PDL: back-to-back launches on different layers' caches sharing the split
+    workspace, eagerly and from a CUDA graph; each result must match the oracle (the early-started
+    kernel may only prefetch cached pages before its predecessor finishes)."""
+    B, Hq, Hkv, D = 6, 32, 8, 128
+    cases = [make_paged_case(B, Hq, Hkv, D, [300 + 17 * i, 1024, 5, 255, 2000, 64], seed=60 + i) for i in range(4)]
+    devs = [to_dev(c) for c in cases]
+    outs = [torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda") for _ in cases]
+
+    def run_all():
+        for d, c, o in zip(devs, cases, outs):
+            b200ops.paged_attn_decode(d["q"][:, 0], d["k_cache"], d["v_cache"], d["k"][:, 0], d["v"][:, 0], d["cos"],
+                                      d["sin"], d["seqlens"], d["table"], softmax_scale=c["scale"], out=o,
+                                      num_splits=3, pdl=mode)
+    wants = []
+    for c in cases:
+        kc, vc = c["k_cache"].clone(), c["v_cache"].clone()
+        wants.append((paged_attention_oracle(c["q"], kc, vc, c["k"], c["v"], c["cos"], c["sin"], c["seqlens"],
+                                             c["table"], c["scale"], True, False)[:, 0], vc))
+    run_all()
+    torch.cuda.synchronize()
+    for o, d, (w, vc) in zip(outs, devs, wants):
+        assert_close(o, w)
+        assert torch.equal(d["v_cache"].cpu(), vc)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        run_all()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        run_all()
+    for o in outs:
+        o.zero_()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for o, (w, _) in zip(outs, wants):
+        assert_close(o, w)

@@ -13,7 +13,7 @@ from _cases import assert_close, make_paged_case, to_dev
 pytestmark = pytest.mark.gpu
 
 
-def check_prefill(case, interleaved=False, causal=True, rotary=True):
+def check_prefill(case, interleaved=False, causal=True, rotary=True, variant=0):
     d = to_dev(case)
     kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
     want = paged_attention_oracle(case["q"], kc_ref, vc_ref, case["k"], case["v"],
@@ -22,7 +22,7 @@ def check_prefill(case, interleaved=False, causal=True, rotary=True):
     got = b200ops.paged_attn_prefill(d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"],
                                      d["cos"] if rotary else None, d["sin"] if rotary else None,
                                      d["seqlens"], d["table"], softmax_scale=case["scale"], causal=causal,
-                                     rotary_interleaved=interleaved)
+                                     rotary_interleaved=interleaved, variant=variant)
     torch.cuda.synchronize()
     assert torch.equal(d["v_cache"].cpu(), vc_ref), "V pages must be bit-exact"
     kd = d["k_cache"].cpu()
@@ -54,6 +54,12 @@ def test_prefill_long_prompt_many_tiles():
     check_prefill(case)
     case = make_paged_case(1, 4, 4, 64, [1100], S_new=1500, seed=22)
     check_prefill(case)
+
+
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
+def test_prefill_smem_operand_variant(D, Hq, Hkv):
+    """variant 1 = the first kernel (Q and P staged in shared memory), kept for A/B measurements."""
+    check_prefill(make_paged_case(2, Hq, Hkv, D, [0, 300], S_new=390, seed=31), variant=1)
 
 
 def test_prefill_interleaved_and_noncausal():

@@ -60,7 +60,7 @@ def _load_gold(golden_dir):
         pytest.skip("flash_attn_gpu.pt not generated yet")
     sys.path.insert(0, golden_dir)
     from make_golden_gpu_lib import appended_rows, inputs_digest
-    return torch.load(path), appended_rows, inputs_digest
+    return torch.load(path, weights_only=False), appended_rows, inputs_digest
 
 
 def test_committed_flash_attn_golden_vectors(golden_dir):

@@ -22,7 +22,7 @@ def traces(golden_dir):
 
 @pytest.fixture(scope="module")
 def ref(golden_dir):
-    return torch.load(os.path.join(golden_dir, "reference_cpu.pt"))
+    return torch.load(os.path.join(golden_dir, "reference_cpu.pt"), weights_only=False)
 
 
 def _state(o):

@@ -60,7 +60,8 @@ def main():
             return e0.elapsed_time(e1) / iters
 
         ms = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out))
-        rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1))
+        ms1 = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=1))
+        rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
         if fa is not None:
             ms_fa = timeit(lambda: fa(q, kc, vc, k=k, v=v, rotary_cos=cos, rotary_sin=sin, cache_seqlens=lens,
                                       block_table=table, causal=True, rotary_interleaved=False))

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--splits", default="1,2,3,4,5,6,8,12,16")
     ap.add_argument("--iters", type=int, default=40)
     ap.add_argument("--no-fa", action="store_true")
+    ap.add_argument("--pdl", type=int, default=0)
     args = ap.parse_args()
     sh = SHAPES[args.shape]
     B, Hq, Hkv, D, ctx = (sh[k] for k in ("B", "Hq", "Hkv", "D", "ctx"))
@@ -98,7 +99,7 @@ def main():
         for S in [int(x) for x in args.splits.split(",")]:
             def fn(i, var=var, S=S):
                 kc, vc = caches[i % n_sets]
-                b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, num_splits=S, variant=var, out=out)
+                b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, num_splits=S, variant=var, out=out, pdl=args.pdl)
             try:
                 us = timeit_graph(fn)
             except Exception as e:  # noqa: BLE001
@@ -125,7 +126,7 @@ def main():
     best = min(results, key=lambda r: r["us"]) if results else None
     print("best:", best)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", f"tune_{args.shape}.json"), "w") as f:
+    with open(os.path.join(ROOT, "gpurun_out", f"tune_{args.shape}{'_pdl%d' % args.pdl if args.pdl else ''}.json"), "w") as f:
         json.dump(dict(shape=sh, algorithmic_bytes=nbytes, results=results, flash_attn=fa, best=best,
                        gpu=torch.cuda.get_device_name(0)), f, indent=1)
 
