@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 4
+#define B200_ABI_VERSION 5
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -220,6 +220,70 @@ typedef struct b200_prefill_args {
 int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D);
 
 int b200_paged_attn_prefill(const b200_prefill_args* args, void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Peer-memory all-reduce fused with the residual add and the RMSNorm that
+ * follow it — replaces, in ONE launch per call site,
+ *   all_reduce(attn_out)  + rmsnorm_residual_gemm(attn_out, h, ln_2.w, ...)
+ *       (core/layer/model_graph.py:210 + :213-216, core/parallel_config.py:65-69)
+ *   all_reduce(mlp_out).add_(residual)  + next layer's rmsnorm_(h, ln_1.w, ...)
+ *       (core/layer/model_graph.py:219 + :143 / final ln_f :222)
+ * Every rank's partial sums x_r [rows, n] bf16 live in a buffer the other
+ * ranks of the node can load from directly (NVLink 5 / NVSwitch peer memory,
+ * exported with b200_ipc_export and mapped with b200_ipc_import).  Each rank
+ * runs the same kernel: a per-CTA flag barrier over peer memory (monotonic
+ * epoch, no reset, CUDA-graph replay safe), then
+ *   s   = bf16( sum_{r=0..world-1} f32(x_r) )          fixed rank order: all
+ *                                                      ranks get identical bits
+ *   res_out = bf16( f32(s) + f32(residual) )           (residual may be NULL)
+ *   ss  = mean( t^2 ),  t = f32(s)+f32(residual)  (ss_rounded = 0, the
+ *         rmsnorm_residual.py:104-108 order) or t = f32(res_out) (ss_rounded
+ *         = 1, the add_ -> rmsnorm_ order of model_graph.py:219,:143)
+ *   y   = bf16( f32(res_out) * rsqrt(ss + eps) * f32(w) )   (w may be NULL:
+ *         no norm, y untouched)
+ * world == 1 runs the same arithmetic on the local x without any barrier.
+ *
+ * Protocol requirements (the Python PeerComm enforces them):
+ *   - all ranks issue the same sequence of calls with the same rows / n;
+ *   - CONSECUTIVE calls must read x from DIFFERENT buffers (two alternating
+ *     slots): the barrier of call k+1 is what tells a rank that its peers
+ *     finished reading the buffer of call k;
+ *   - flags: uint32 [B200_AR_MAX_CTAS][B200_AR_MAX_WORLD] per rank, zeroed
+ *     once; epoch: LOCAL uint32 [B200_AR_MAX_CTAS + 1], zeroed once; word
+ *     [B200_AR_MAX_CTAS] is set to 1 if a wait timed out (peer missing).
+ * ------------------------------------------------------------------------ */
+#define B200_AR_MAX_WORLD 8
+#define B200_AR_MAX_CTAS  1024
+
+typedef struct b200_ar_args {
+    const void* x_peers[B200_AR_MAX_WORLD];  /* rank r's partial sums, bf16 [rows, n] (entry `rank` is local) */
+    void*       flag_peers[B200_AR_MAX_WORLD]; /* rank r's flag array (entry `rank` is local)                 */
+    void*       epoch;        /* local epoch counters + error word                 */
+    const void* residual;     /* local bf16 [rows, n] or NULL                      */
+    const void* weight;       /* norm weight [n] (w_dtype) or NULL = no norm       */
+    void*       y;            /* bf16 [rows, n] normed output (NULL iff weight NULL) */
+    void*       res_out;      /* bf16 [rows, n] reduced (+ residual) output        */
+    int64_t rows, n;
+    int64_t stride_x, stride_r, stride_y, stride_res;   /* elements */
+    float   eps;
+    int32_t w_dtype;          /* B200_DT_*                                         */
+    int32_t rank, world;      /* world in {1, 2, 4, 8}                             */
+    int32_t ss_rounded;       /* see above                                         */
+    int32_t timeout_ms;       /* flag wait bound; 0 = default 2000                 */
+} b200_ar_args;
+
+int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
+
+/* Peer-memory plumbing (init time only; these DO allocate / synchronise).
+ * b200_comm_alloc: cudaMalloc + zero fill of an IPC-exportable buffer on the current device.
+ * b200_ipc_export: 64-byte handle another process of the node can map.
+ * b200_ipc_import: map a peer's buffer (enables peer access lazily); b200_ipc_close unmaps. */
+#define B200_IPC_HANDLE_BYTES 64
+int b200_comm_alloc(int64_t bytes, void** dev_ptr);
+int b200_comm_free(void* dev_ptr);
+int b200_ipc_export(const void* dev_ptr, void* handle_out);
+int b200_ipc_import(const void* handle, void** peer_ptr);
+int b200_ipc_close(void* peer_ptr);
 
 #ifdef __cplusplus
 }

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 
 class DecodeArgs(C.Structure):
@@ -63,6 +63,21 @@ class PrefillArgs(C.Structure):
     ]
 
 
+AR_MAX_WORLD, AR_MAX_CTAS, IPC_HANDLE_BYTES = 8, 1024, 64
+
+
+class ArArgs(C.Structure):
+    """struct b200_ar_args (include/b200_abi.h)."""
+    _fields_ = [
+        ("x_peers", _vp * AR_MAX_WORLD), ("flag_peers", _vp * AR_MAX_WORLD),
+        ("epoch", _vp), ("residual", _vp), ("weight", _vp), ("y", _vp), ("res_out", _vp),
+        ("rows", _i64), ("n", _i64),
+        ("stride_x", _i64), ("stride_r", _i64), ("stride_y", _i64), ("stride_res", _i64),
+        ("eps", _f32), ("w_dtype", _i32), ("rank", _i32), ("world", _i32),
+        ("ss_rounded", _i32), ("timeout_ms", _i32),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200_abi.h declares
 SIGNATURES = {
     "b200_version": (C.c_int, []),
@@ -79,6 +94,12 @@ SIGNATURES = {
     "b200_lse_combine": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp]),
     "b200_prefill_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200_paged_attn_prefill": (C.c_int, [C.POINTER(PrefillArgs), _vp]),
+    "b200_allreduce_residual_rmsnorm": (C.c_int, [C.POINTER(ArArgs), _vp]),
+    "b200_comm_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
+    "b200_comm_free": (C.c_int, [_vp]),
+    "b200_ipc_export": (C.c_int, [_vp, _vp]),
+    "b200_ipc_import": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "b200_ipc_close": (C.c_int, [_vp]),
 }
 
 

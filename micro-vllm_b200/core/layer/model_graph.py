@@ -16,8 +16,15 @@ the hot path this repo owns:
   * an un-captured batch size runs eagerly against the REAL block table (the reference
     substitutes an all-zero table there, :158/:257-258, which is only right during warm-up).
 
-GEMMs stay ``torch.matmul(..., out=)`` (cuBLAS; out of scope) and the two
-all-reduces per layer stay NCCL (``core.parallel_config.all_reduce``).
+  * the two all-reduces of a layer and the elementwise kernels behind them are ONE launch each
+    (``b200_allreduce_residual_rmsnorm``): ``all_reduce(attn_out)`` + ``rmsnorm_residual_gemm``
+    (:210-216) and ``all_reduce(mlp_out).add_(residual)`` + the NEXT layer's ``rmsnorm_`` (:219,
+    :143; the final ``ln_f`` :222 for the last layer).  With TP the o_proj / down_proj GEMMs write
+    straight into NVLink peer-memory slots and the kernel sums all ranks' slots itself
+    (``b200ops.comm.PeerComm``); ``B200_FUSED_ALLREDUCE=0`` keeps NCCL for the reduction.  The
+    arithmetic (rounding points included) is the reference sequence's.
+
+GEMMs stay ``torch.matmul(..., out=)`` (cuBLAS; out of scope).
 """
 import logging
 from typing import Dict, List
@@ -26,9 +33,9 @@ import torch
 
 import b200ops
 from core.paged_attention import PagedAttention
-from core.parallel_config import all_reduce, get_rank, get_world_size
+from b200ops.comm import allreduce_residual_rmsnorm_local
+from core.parallel_config import all_reduce, get_rank, get_world_size, peer_comm
 from kernel.rmsnorm_add import rmsnorm_
-from kernel.rmsnorm_residual import rmsnorm_residual_gemm
 from kernel.swiglu import swiglu_gemm
 from .rope import RoPE
 
@@ -114,11 +121,19 @@ class ModelGraphRunner:
         self._gate_up = torch.empty((mb, gu_dim), dtype=dt, device=dev)
         self._swiglu_out = torch.empty((mb, gu_dim // 2), dtype=dt, device=dev)
         self._mlp_out = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        self._h = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
+        # TP: the two GEMMs whose outputs are summed over ranks write into peer-visible slots
+        self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
+        if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
+            self._comm = None
+        if self._comm is not None:
+            self._attn_out = self._comm.slot(0, mb, self.hidden_dim)
+            self._mlp_out = self._comm.slot(1, mb, self.hidden_dim)
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
 
     # ------------------------------------------------------------------ per-layer pieces
-    def _qkv_proj(self, h, block, bs):
-        rmsnorm_(h, block.ln_1.weight, self._normed[:bs], block.ln_1.eps)
+    def _qkv_proj(self, block, bs):
+        """QKV projection of ``self._normed[:bs]`` (the ln_1 norm was fused into the previous launch)."""
         qkv = self._qkv[:bs]
         torch.matmul(self._normed[:bs], block.attn._qkv_w, out=qkv)
         if block.attn._qkv_b is not None:
@@ -150,17 +165,39 @@ class ModelGraphRunner:
         return self._mlp_out[:bs]
 
     # ------------------------------------------------------------------ decode step
+    def _reduce_add_norm(self, slot, x, residual, norm, y, res_out, ss_rounded):
+        """res_out = all_reduce(x) + residual;  y = rmsnorm(res_out) * norm.weight — one launch.
+        ``norm`` None skips the norm.  ``x`` is peer slot ``slot`` when the communicator is up."""
+        w = norm.weight if norm is not None else None
+        eps = norm.eps if norm is not None else 0.0
+        if self._comm is not None:
+            self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
+                                                  y if norm is not None else None, res_out, eps, ss_rounded)
+        else:
+            all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
+            allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,
+                                             ss_rounded)
+
     def decode(self, input_ids, bs, cache_manager, use_graph_cache):
-        h = self.model.transformer.wte(input_ids)
+        tr = self.model.transformer
+        h = tr.wte(input_ids)
+        normed, residual, h_buf = self._normed[:bs], self._residual[:bs], self._h[:bs]
+        rmsnorm_(h, tr.h[0].ln_1.weight, normed, tr.h[0].ln_1.eps)
+        ln_f = tr.ln_f
+        fuse_ln_f = bool(getattr(ln_f, "b200_kernel_norm", False))      # any other module is called as is
         for layer_idx in range(self.num_layers):
-            block = self.model.transformer.h[layer_idx]
-            qkv = self._qkv_proj(h, block, bs)
-            attn_out = all_reduce(self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache))
-            rmsnorm_residual_gemm(attn_out, h, block.ln_2.weight, self._normed[:bs], self._residual[:bs],
-                                  block.ln_2.eps)
-            mlp_out = self._ffn(self._normed[:bs], block, bs)
-            h = all_reduce(mlp_out).add_(self._residual[:bs])
-        return self.model.lm_head(self.model.transformer.ln_f(h))
+            block = tr.h[layer_idx]
+            qkv = self._qkv_proj(block, bs)
+            attn_out = self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache)
+            # all_reduce + rmsnorm_residual_gemm (reference :210-216): sum of squares of the unrounded sum
+            self._reduce_add_norm(0, attn_out, h, block.ln_2, normed, residual, ss_rounded=False)
+            mlp_out = self._ffn(normed, block, bs)
+            # all_reduce(mlp_out).add_(residual) + the next rmsnorm_ (reference :219, :143 / :222)
+            last = layer_idx + 1 == self.num_layers
+            nxt = (ln_f if fuse_ln_f else None) if last else tr.h[layer_idx + 1].ln_1
+            self._reduce_add_norm(1, mlp_out, residual, nxt, normed, h_buf, ss_rounded=True)
+            h = h_buf
+        return self.model.lm_head(normed if fuse_ln_f else ln_f(h))
 
     def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32]):
         """3 eager warm-ups then ``torch.cuda.graph`` per batch size (reference :225-253)."""

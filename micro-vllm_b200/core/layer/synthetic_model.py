@@ -40,6 +40,7 @@ SHAPES = {
 
 class RMSNormModule(nn.Module):
     """``weight`` + ``eps`` holder; calling it runs the sm_100a RMSNorm kernel (used as ``ln_f``)."""
+    b200_kernel_norm = True        # same arithmetic as kernel.rmsnorm_add.rmsnorm: the decode runner may fuse it
 
     def __init__(self, hidden: int, eps: float, dtype, device):
         super().__init__()

@@ -14,7 +14,7 @@ import os
 import torch
 import torch.distributed as dist
 
-_state = {"world_group": None, "parallel_group": None, "is_main_rank": False}
+_state = {"world_group": None, "parallel_group": None, "is_main_rank": False, "peer_comm": None}
 
 
 def setup():
@@ -62,3 +62,22 @@ def all_reduce(input_):
 def barrier():
     if get_world_size() > 1 and dist.is_initialized():
         dist.barrier(group=get_group() or dist.group.WORLD)
+
+
+def peer_comm(slot_bytes: int):
+    """The node-local NVLink peer-memory communicator behind the fused all-reduce + residual +
+    RMSNorm kernel (``b200ops.comm.PeerComm``), created on first use and grown on demand; ``None``
+    for single-process runs, on CPU (gloo), for world sizes other than 2 / 4 / 8, or when
+    ``B200_FUSED_ALLREDUCE=0`` selects the plain NCCL ``all_reduce`` + elementwise kernels
+    (the reference's sequence, model_graph.py:210-219)."""
+    if get_world_size() not in (2, 4, 8) or not torch.cuda.is_available():
+        return None
+    if os.environ.get("B200_FUSED_ALLREDUCE", "1") == "0":
+        return None
+    comm = _state["peer_comm"]
+    if comm is None or comm.slot_bytes < slot_bytes:
+        from b200ops.comm import PeerComm
+        # an outgrown communicator stays mapped: captured graphs may hold its addresses
+        comm = PeerComm(slot_bytes, group=get_group() or dist.group.WORLD)
+        _state["peer_comm"] = comm
+    return comm

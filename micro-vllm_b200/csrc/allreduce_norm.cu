@@ -1,0 +1,298 @@
+// One-shot all-reduce over NVLink peer memory fused with the residual add and the RMSNorm
+// that follow it on the decode path:
+//   all_reduce(attn_out) -> rmsnorm_residual_gemm        (reference: core/layer/model_graph.py:210-216)
+//   all_reduce(mlp_out).add_(residual) -> rmsnorm_(h)     (reference: core/layer/model_graph.py:219, :143, :222)
+//   all_reduce itself                                     (reference: core/parallel_config.py:65-69)
+//
+// Every rank launches the same kernel.  One CTA owns whole rows: it (1) signals "my partial sums
+// are written" into every peer's flag array and waits for every peer's signal (release/acquire at
+// system scope, a monotonically increasing epoch instead of a reset, so a captured CUDA graph can be
+// replayed forever), (2) loads its rows from all `world` buffers with 128-bit loads — world x 16 B
+// in flight per thread, the remote ones straight over NVLink 5 / NVSwitch — and sums them in fp32
+// in rank order, so every rank computes bit-identical results, (3) adds the residual, keeps the row in
+// registers for the sum of squares and writes res_out and y.  The decode activations are tiny
+// ([64, 8192] bf16 = 1 MiB), so the one-shot form (every rank reads everything, 1 barrier) beats a
+// reduce-scatter/all-gather pair (2 barriers); the host side falls back to NCCL above a few MiB.
+//
+// There is no trailing barrier: the caller alternates between two input buffers, and the barrier of
+// call k+1 is the proof that every peer finished reading the buffer of call k (b200_abi.h).
+#include "common.cuh"
+
+namespace b200 {
+
+struct ArParams {
+    const __nv_bfloat16* x[B200_AR_MAX_WORLD];
+    uint32_t* flags[B200_AR_MAX_WORLD];
+    uint32_t* epoch;
+    const __nv_bfloat16* r;
+    const void* w;
+    __nv_bfloat16* y;
+    __nv_bfloat16* res_out;
+    int64_t rows, n, sx, sr, sy, sres;
+    float eps;
+    int rank, ss_rounded;
+    long long timeout_cycles;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// peer data: never served from a stale L1 line (the same addresses carry new data every step)
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+    uint4 r;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+template <typename WT> struct ArW;
+template <> struct ArW<__nv_bfloat16> {
+    static __device__ __forceinline__ void load8(const void* w, int64_t e, float (&o)[8]) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)w + e));
+        const uint32_t* p = &v.x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { o[2 * i] = bf16lo(p[i]); o[2 * i + 1] = bf16hi(p[i]); }
+    }
+};
+template <> struct ArW<float> {
+    static __device__ __forceinline__ void load8(const void* w, int64_t e, float (&o)[8]) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>((const float*)w + e));
+        const float4 b = __ldg(reinterpret_cast<const float4*>((const float*)w + e + 4));
+        o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+    }
+};
+
+template <int WS, int VPT, typename WT>
+__global__ void __launch_bounds__(1024)
+allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
+    __shared__ float red[32];
+    const int bid = blockIdx.x;
+    const int T = blockDim.x;
+    const int nvec = (int)(p.n >> 3);
+
+    if (WS > 1) {
+        const uint32_t e = p.epoch[bid] + 1u;
+        if (threadIdx.x < WS) {
+            const int peer = threadIdx.x;
+            // everything this rank's stream wrote before this kernel (the GEMM that produced x) is ordered
+            // before the flag by the release; the peer's acquire + its CTA barrier orders its loads after it
+            st_release_sys(p.flags[peer] + bid * B200_AR_MAX_WORLD + p.rank, e);
+            const uint32_t* mine = p.flags[p.rank] + bid * B200_AR_MAX_WORLD + peer;
+            const long long t0 = clock64();
+            while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+                if (clock64() - t0 > p.timeout_cycles) {          // a peer never arrived: flag it, do not hang the GPU
+                    atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u);
+                    break;
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) p.epoch[bid] = e;
+    }
+
+    const bool has_r = p.r != nullptr;
+    const bool norm = p.w != nullptr;
+    for (int64_t row = bid; row < p.rows; row += gridDim.x) {
+        float ss = 0.0f;
+        float f[VPT][8];
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                // world x 16 B in flight per thread (VPT = 1 covers n <= 8192: the whole row is in flight at once)
+                uint4 xv[WS];
+                uint4 rv = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+                for (int k = 0; k < WS; ++k) {
+                    const __nv_bfloat16* src = p.x[k] + row * p.sx + (int64_t)v * 8;
+                    xv[k] = (WS > 1) ? ld_peer_v4(src) : ld_v4(src);
+                }
+                if (has_r) rv = ld_v4(p.r + row * p.sr + (int64_t)v * 8);
+                uint4 ro;
+                uint32_t* pro = &ro.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float a = bf16lo((&xv[0].x)[k]), b = bf16hi((&xv[0].x)[k]);
+#pragma unroll
+                    for (int q = 1; q < WS; ++q) {
+                        a += bf16lo((&xv[q].x)[k]);
+                        b += bf16hi((&xv[q].x)[k]);
+                    }
+                    if (WS > 1) {                     // what all_reduce hands back is a bf16 tensor
+                        const uint32_t s = pack_bf16(a, b);
+                        a = bf16lo(s); b = bf16hi(s);
+                    }
+                    if (has_r) {
+                        a += bf16lo((&rv.x)[k]);
+                        b += bf16hi((&rv.x)[k]);
+                    }
+                    const uint32_t pk = pack_bf16(a, b);
+                    pro[k] = pk;
+                    const float ar = bf16lo(pk), br = bf16hi(pk);
+                    if (p.ss_rounded) { ss += ar * ar; ss += br * br; }
+                    else              { ss += a * a;   ss += b * b; }
+                    f[i][2 * k] = ar; f[i][2 * k + 1] = br;
+                }
+                st_na_v4(p.res_out + row * p.sres + (int64_t)v * 8, ro);
+            }
+        }
+        if (!norm) continue;
+        // block reduction (all threads of the CTA take this path together: `norm` is uniform)
+        {
+            const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+            const int nw = (T + 31) >> 5;
+            ss = warp_sum(ss);
+            if (nw > 1) {
+                __syncthreads();                      // red[] may still be read by the previous row
+                if (lane == 0) red[wid] = ss;
+                __syncthreads();
+                float t = (lane < nw) ? red[lane] : 0.0f;
+                ss = warp_sum(t);
+            }
+        }
+        const float rrms = rsqrtf(ss / (float)p.n + p.eps);
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                float wf[8];
+                ArW<WT>::load8(p.w, (int64_t)v * 8, wf);
+                uint4 o;
+                uint32_t* po = &o.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
+                st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
+            }
+        }
+    }
+}
+
+template <int WS, typename WT>
+static int launch_ar(const ArParams& p, cudaStream_t st) {
+    const int64_t nvec = p.n / 8;
+    const unsigned grid = (unsigned)(p.rows < B200_AR_MAX_CTAS ? p.rows : B200_AR_MAX_CTAS);
+    if (nvec <= 1024) {
+        const int threads = (int)((nvec + 31) & ~31LL);
+        allreduce_residual_rmsnorm_kernel<WS, 1, WT><<<grid, threads, 0, st>>>(p);
+    } else {
+        int threads = (int)((nvec + 1) / 2);
+        threads = (threads + 31) & ~31;
+        allreduce_residual_rmsnorm_kernel<WS, 2, WT><<<grid, threads, 0, st>>>(p);
+    }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename WT>
+static int dispatch_ws(int world, const ArParams& p, cudaStream_t st) {
+    switch (world) {
+        case 1: return launch_ar<1, WT>(p, st);
+        case 2: return launch_ar<2, WT>(p, st);
+        case 4: return launch_ar<4, WT>(p, st);
+        case 8: return launch_ar<8, WT>(p, st);
+    }
+    B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: world=%d (1, 2, 4 or 8)", world);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stream) {
+    if (!a) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: null args");
+    if (a->world < 1 || a->world > B200_AR_MAX_WORLD || a->rank < 0 || a->rank >= a->world)
+        B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: rank=%d world=%d", a->rank, a->world);
+    if (!a->res_out) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: res_out is NULL");
+    if ((a->weight == nullptr) != (a->y == nullptr))
+        B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: weight and y must both be given or both be NULL");
+    if (a->rows < 0 || a->n <= 0) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: rows=%lld n=%lld",
+                                            (long long)a->rows, (long long)a->n);
+    if (a->n % 8 != 0 || a->n > 16384)
+        B200_FAIL(B200_E_SHAPE, "allreduce_residual_rmsnorm: n=%lld (multiple of 8, <= 16384)", (long long)a->n);
+    ArParams p{};
+    for (int r = 0; r < a->world; ++r) {
+        if (!a->x_peers[r]) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: x_peers[%d] is NULL", r);
+        if (!aligned16(a->x_peers[r])) B200_FAIL(B200_E_ALIGN, "allreduce_residual_rmsnorm: x_peers[%d] not 16-byte aligned", r);
+        p.x[r] = (const __nv_bfloat16*)a->x_peers[r];
+        if (a->world > 1) {
+            if (!a->flag_peers[r]) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: flag_peers[%d] is NULL", r);
+            p.flags[r] = (uint32_t*)a->flag_peers[r];
+        }
+    }
+    if (a->world > 1 && !a->epoch) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: epoch is NULL");
+    if (!aligned16(a->res_out) || (a->residual && !aligned16(a->residual)) || (a->y && !aligned16(a->y)) ||
+        (a->weight && !aligned16(a->weight)))
+        B200_FAIL(B200_E_ALIGN, "allreduce_residual_rmsnorm: pointers must be 16-byte aligned");
+    if (a->stride_x % 8 || a->stride_res % 8 || (a->residual && a->stride_r % 8) || (a->y && a->stride_y % 8))
+        B200_FAIL(B200_E_ALIGN, "allreduce_residual_rmsnorm: row strides must be multiples of 8 elements");
+    if (a->rows == 0) return 0;
+    p.epoch = (uint32_t*)a->epoch;
+    p.r = (const __nv_bfloat16*)a->residual;
+    p.w = a->weight;
+    p.y = (__nv_bfloat16*)a->y;
+    p.res_out = (__nv_bfloat16*)a->res_out;
+    p.rows = a->rows; p.n = a->n;
+    p.sx = a->stride_x; p.sr = a->stride_r; p.sy = a->stride_y; p.sres = a->stride_res;
+    p.eps = a->eps; p.rank = a->rank; p.ss_rounded = a->ss_rounded ? 1 : 0;
+    const int ms = a->timeout_ms > 0 ? a->timeout_ms : 2000;
+    p.timeout_cycles = (long long)ms * 2000000LL;          // ~2 GHz SM clock upper bound
+    cudaStream_t st = (cudaStream_t)stream;
+    if (a->weight && a->w_dtype == B200_DT_F32) return dispatch_ws<float>(a->world, p, st);
+    if (!a->weight || a->w_dtype == B200_DT_BF16) return dispatch_ws<__nv_bfloat16>(a->world, p, st);
+    B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
+}
+
+// ------------------------------------------------------------------ peer-memory plumbing (init time)
+extern "C" int b200_comm_alloc(int64_t bytes, void** dev_ptr) {
+    if (!dev_ptr) B200_FAIL(B200_E_NULL, "comm_alloc: null out pointer");
+    if (bytes <= 0) B200_FAIL(B200_E_RANGE, "comm_alloc: bytes=%lld", (long long)bytes);
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, (size_t)bytes);
+    if (e != cudaSuccess) { set_error("comm_alloc: cudaMalloc(%lld): %s", (long long)bytes, cudaGetErrorString(e)); return (int)e; }
+    e = cudaMemset(p, 0, (size_t)bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { cudaFree(p); set_error("comm_alloc: memset: %s", cudaGetErrorString(e)); return (int)e; }
+    *dev_ptr = p;
+    return 0;
+}
+
+extern "C" int b200_comm_free(void* dev_ptr) {
+    if (!dev_ptr) return 0;
+    cudaError_t e = cudaFree(dev_ptr);
+    if (e != cudaSuccess) { set_error("comm_free: %s", cudaGetErrorString(e)); return (int)e; }
+    return 0;
+}
+
+extern "C" int b200_ipc_export(const void* dev_ptr, void* handle_out) {
+    if (!dev_ptr || !handle_out) B200_FAIL(B200_E_NULL, "ipc_export: null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == B200_IPC_HANDLE_BYTES, "handle size");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(dev_ptr));
+    if (e != cudaSuccess) { set_error("ipc_export: %s", cudaGetErrorString(e)); return (int)e; }
+    memcpy(handle_out, &h, sizeof(h));
+    return 0;
+}
+
+extern "C" int b200_ipc_import(const void* handle, void** peer_ptr) {
+    if (!handle || !peer_ptr) B200_FAIL(B200_E_NULL, "ipc_import: null pointer");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { set_error("ipc_import: %s", cudaGetErrorString(e)); return (int)e; }
+    *peer_ptr = p;
+    return 0;
+}
+
+extern "C" int b200_ipc_close(void* peer_ptr) {
+    if (!peer_ptr) return 0;
+    cudaError_t e = cudaIpcCloseMemHandle(peer_ptr);
+    if (e != cudaSuccess) { set_error("ipc_close: %s", cudaGetErrorString(e)); return (int)e; }
+    return 0;
+}

@@ -49,3 +49,28 @@ def bf16_ulp_diff(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
         i = t.contiguous().view(torch.int16).to(torch.int32) & 0xFFFF
         return torch.where(i >= 0x8000, 0x8000 - i, i)
     return (key(a.to(torch.bfloat16)) - key(b.to(torch.bfloat16))).abs()
+
+
+def allreduce_residual_rmsnorm_oracle(parts, residual, w, eps: float, ss_rounded: bool):
+    """The two all-reduce call sites of the decode loop with what follows them:
+    core/layer/model_graph.py:210 + :213-216 (``all_reduce(attn_out)`` then
+    ``rmsnorm_residual_gemm``: sum of squares from the UNROUNDED x + r, ``ss_rounded=False``) and
+    :219 + :143 / :222 (``all_reduce(mlp_out).add_(residual)`` then ``rmsnorm_``: the norm reads the
+    bf16-ROUNDED sum, ``ss_rounded=True``).  ``parts`` = the per-rank partial sums (bf16); the
+    all-reduce result is a bf16 tensor (core/parallel_config.py:65-69), summed here in fp32 in rank
+    order and rounded once (NCCL's own association order is unspecified).  Returns (y, res_out);
+    ``w`` None skips the norm (y None)."""
+    s = parts[0].float()
+    for p in parts[1:]:
+        s = s + p.float()
+    if len(parts) > 1:
+        s = _bf16(s).float()
+    if residual is not None:
+        s = s + residual.float()
+    res = _bf16(s)
+    if w is None:
+        return None, res
+    n = res.shape[-1]
+    t = res.float() if ss_rounded else s
+    rrms = torch.rsqrt(t.pow(2).sum(-1, keepdim=True) / n + eps)
+    return _bf16(res.float() * rrms * w.float()), res

@@ -29,15 +29,16 @@ def test_struct_layout_matches_header():
     """ctypes struct sizes must match the C structs (checked by compiling a tiny C probe)."""
     import subprocess, tempfile
     from b200ops import _lib
-    src = '#include <stdio.h>\n#include "b200_abi.h"\nint main(){printf("%zu %zu\\n", sizeof(b200_decode_args), sizeof(b200_prefill_args));return 0;}\n'
+    src = '#include <stdio.h>\n#include "b200_abi.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(b200_decode_args), sizeof(b200_prefill_args), sizeof(b200_ar_args));return 0;}\n'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "p.c")
         open(c, "w").write(src)
         exe = os.path.join(d, "p")
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
-        dec, pre = map(int, subprocess.check_output([exe]).split())
+        dec, pre, ar = map(int, subprocess.check_output([exe]).split())
     assert ctypes.sizeof(_lib.DecodeArgs) == dec
     assert ctypes.sizeof(_lib.PrefillArgs) == pre
+    assert ctypes.sizeof(_lib.ArArgs) == ar
 
 
 def test_argument_errors_without_device():
@@ -62,6 +63,37 @@ def test_argument_errors_without_device():
     assert lib.b200_decode_workspace_bytes(32, 32, 8, 128, 4) == 65536 * 4 + 32 * 32 * 4 * 4 + 32 * 32 * 4 * 128 * 4
     assert lib.b200_decode_workspace_bytes(32, 30, 8, 128, 4) == -1
     assert lib.b200_prefill_workspace_bytes(2, 128, 32, 128) == 2 * 128 * 32 * 128 * 2
+
+
+def test_allreduce_norm_argument_errors_without_device():
+    from b200ops import _lib
+    lib = _lib.lib
+    assert lib.b200_allreduce_residual_rmsnorm(None, None) == _lib.E_NULL
+    a = _lib.ArArgs()
+    a.world, a.rank, a.res_out, a.epoch = 3, 0, 0x1000, 0x1000
+    for k in range(3):
+        a.x_peers[k] = a.flag_peers[k] = 0x1000
+    a.rows, a.n, a.stride_x, a.stride_res = 1, 64, 64, 64
+    assert lib.b200_allreduce_residual_rmsnorm(ctypes.byref(a), None) == _lib.E_UNSUPPORTED     # world 3
+    a.world, a.n = 2, 60
+    assert lib.b200_allreduce_residual_rmsnorm(ctypes.byref(a), None) == _lib.E_SHAPE           # n % 8
+    a.n, a.rank = 64, 2
+    assert lib.b200_allreduce_residual_rmsnorm(ctypes.byref(a), None) == _lib.E_RANGE           # rank >= world
+    a.rank, a.weight = 0, 0x1000
+    assert lib.b200_allreduce_residual_rmsnorm(ctypes.byref(a), None) == _lib.E_NULL            # weight without y
+    assert lib.b200_comm_alloc(0, None) == _lib.E_NULL
+    assert lib.b200_ipc_export(None, None) == _lib.E_NULL and lib.b200_ipc_import(None, None) == _lib.E_NULL
+    assert lib.b200_comm_free(None) == 0 and lib.b200_ipc_close(None) == 0
+
+
+def test_peer_comm_requires_process_group():
+    import torch
+    from b200ops.comm import PeerComm, allreduce_residual_rmsnorm_local
+    with pytest.raises(AssertionError):
+        PeerComm(1 << 20)                                   # no torch.distributed: nothing to rendezvous with
+    x = torch.zeros(2, 16, dtype=torch.bfloat16)
+    with pytest.raises(AssertionError):                     # CPU tensors are refused, no fallback
+        allreduce_residual_rmsnorm_local(x, x, torch.ones(16, dtype=torch.bfloat16), x.clone(), x.clone(), 1e-6, False)
 
 
 def test_ops_refuse_cpu_tensors():
