@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 5
+#define B200_ABI_VERSION 6
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -161,8 +161,17 @@ typedef struct b200_decode_args {
 /* with PDL: release the dependent kernel after the streaming loop instead of at kernel start */
 #define B200_DECODE_FLAG_PDL_LATE 2
 
+/* Balanced (stream-K) scheduling: a fixed grid of #SMs x resident CTAs, independent of the
+ * lengths; the 64-token chunks of all (sequence, kv head) pairs are laid end to end and cut into
+ * equal shares, one per CTA, computed on the device from cache_seqlens, so ragged batches
+ * (continuous batching) and small batches keep every SM equally busy.  num_splits is ignored;
+ * the workspace must hold b200_decode_balanced_workspace_bytes(D) bytes (same zero-once rule);
+ * B <= 512. */
+#define B200_DECODE_FLAG_BALANCED 4
+
 int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
                                     int32_t num_splits);
+int64_t b200_decode_balanced_workspace_bytes(int32_t D);
 
 int b200_paged_attn_decode(const b200_decode_args* args, void* stream);
 

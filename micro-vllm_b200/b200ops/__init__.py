@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "decode_num_splits", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
 ]
 
 
@@ -128,6 +128,23 @@ def decode_num_splits(batch: int, kv_heads: int, capacity_tokens: int, n_sm: int
     return int(max(1, min(want, cap, 128)))
 
 
+_BALANCED_ENV = None
+
+
+def decode_use_balanced(batch: int, kv_heads: int, n_sm: int = 148) -> bool:
+    """Whether the persistent stream-K form is the default for this launch shape (launch-time
+    constants only).  ``B200_DECODE_BALANCED`` = 0 / 1 forces it off / on (tuning)."""
+    global _BALANCED_ENV
+    if _BALANCED_ENV is None:
+        import os
+        _BALANCED_ENV = os.environ.get("B200_DECODE_BALANCED", "")
+    if batch > _lib.DECODE_BALANCED_MAX_B:
+        return False
+    if _BALANCED_ENV in ("0", "1"):
+        return _BALANCED_ENV == "1"
+    return False
+
+
 _RETIRED: list = []
 
 
@@ -152,12 +169,15 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
                       softmax_scale: Optional[float] = None, rotary_interleaved: bool = False,
                       num_splits: int = 0, out: Optional[torch.Tensor] = None,
                       softmax_lse: Optional[torch.Tensor] = None, variant: int = 0,
-                      pdl: int = 0) -> torch.Tensor:
+                      pdl: int = 0, balanced: Optional[bool] = None) -> torch.Tensor:
     """q [B, Hq, D]; k_new/v_new [B, Hkv, D]; caches [n_blocks, block_size, Hkv, D];
     returns out [B, Hq, D] (allocated unless given).  ``pdl`` = 1 / 2 launches with programmatic
     stream serialization, releasing the next kernel at start / after the streaming loop (see
     B200_DECODE_FLAG_PDL in b200_abi.h for the precondition; measured slower than a plain launch on
-    back-to-back decode kernels, so it is off by default)."""
+    back-to-back decode kernels, so it is off by default).  ``balanced`` selects the persistent
+    stream-K form (fixed grid, equal shares of all sequences' chunks per CTA, schedule derived on
+    the device from ``cache_seqlens``: right for ragged and small batches); ``None`` = the
+    :func:`decode_use_balanced` heuristic; an explicit ``num_splits`` > 0 keeps the split-KV grid."""
     _req_cuda(q, k_cache, v_cache, k_new, v_new, rotary_cos, rotary_sin, cache_seqlens, block_table)
     B, Hq, D = q.shape
     n_blocks, block_size, Hkv, Dc = k_cache.shape
@@ -198,15 +218,24 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     a.kc_stride_blk, a.kc_stride_tok, a.kc_stride_h = k_cache.stride(0), k_cache.stride(1), k_cache.stride(2)
     a.vc_stride_blk, a.vc_stride_tok, a.vc_stride_h = v_cache.stride(0), v_cache.stride(1), v_cache.stride(2)
     a.bt_stride_b = block_table.stride(0)
+    if balanced is None:
+        balanced = num_splits <= 0 and not pdl and decode_use_balanced(B, Hkv, sm_count(q.device))
     if num_splits <= 0:
-        num_splits = decode_num_splits(B, Hkv, block_table.shape[1] * block_size, sm_count(q.device))
+        num_splits = 1 if balanced else decode_num_splits(B, Hkv, block_table.shape[1] * block_size,
+                                                          sm_count(q.device))
     a.num_splits, a.variant = int(num_splits), int(variant)
     a.flags = 0 if not pdl else (_lib.DECODE_FLAG_PDL | (_lib.DECODE_FLAG_PDL_LATE if int(pdl) == 2 else 0))
-    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 1.0 / math.sqrt(D)
-    if num_splits > 1:
+    if balanced:
+        assert not pdl, "paged_attn_decode: the balanced form has no PDL variant"
+        a.flags |= _lib.DECODE_FLAG_BALANCED
+        need = lib.b200_decode_balanced_workspace_bytes(D)
+        ws = _workspace(q.device, need, "decode")
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+    elif num_splits > 1:
         need = lib.b200_decode_workspace_bytes(B, Hq, Hkv, D, num_splits)
         ws = _workspace(q.device, need, "decode")
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 1.0 / math.sqrt(D)
     check(lib.b200_paged_attn_decode(C.byref(a), _stream()), "b200_paged_attn_decode")
     return out
 

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class DecodeArgs(C.Structure):
@@ -40,6 +40,8 @@ class DecodeArgs(C.Structure):
 
 DECODE_FLAG_PDL = 1
 DECODE_FLAG_PDL_LATE = 2
+DECODE_FLAG_BALANCED = 4
+DECODE_BALANCED_MAX_B = 512
 
 
 class PrefillArgs(C.Structure):
@@ -90,6 +92,7 @@ SIGNATURES = {
     "b200_store_kvcache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _i64,
                                       _i64, _i64, _i64, _i64, _i64, _vp]),
     "b200_decode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32, _i32]),
+    "b200_decode_balanced_workspace_bytes": (_i64, [_i32]),
     "b200_paged_attn_decode": (C.c_int, [C.POINTER(DecodeArgs), _vp]),
     "b200_lse_combine": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp]),
     "b200_prefill_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),

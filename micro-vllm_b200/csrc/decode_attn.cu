@@ -93,34 +93,39 @@ __device__ __forceinline__ uint32_t swz(int r, int c) {
     return (uint32_t)(r * (CPR * 16) + ((c ^ (r & 7)) << 4));
 }
 
-template <class C>
-__global__ void __launch_bounds__(C::THREADS, C::MINB)
-paged_decode_kernel(const __grid_constant__ DecodeParams p) {
+// One piece of work = chunks [c0, c1) of the tokens of ONE (sequence b, kv head kvh, head group grp).
+struct Piece {
+    int b, kvh, grp;
+    int c0, c1;            // chunk range (chunks of C::CH tokens)
+    int n_chunks;          // chunks of the whole sequence (the piece with c1 == n_chunks owns the new token)
+    int pos, seqlen_k;     // cache_seqlens[b], keys attended (pos + 1 with a new token)
+};
+
+// Streams one piece and merges the CTA's warps; sink(g, d, val, lse) receives the normalised partial
+// output of head g of the group (val for element d, lse = natural-log sum over the piece).  Uses all
+// of the CTA's shared memory; the caller must __syncthreads() before the next piece.
+template <class C, class Sink>
+__device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* smem, const Piece& pc, bool pdl, Sink&& sink) {
     constexpr int D = C::D, TPS = C::TPS, STAGES = C::STAGES, CPR = C::CPR, RPI = C::RPI;
-    extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_kv = smem;                               // [NWARPS][STAGES][K tile | V tile]
     uint8_t* s_q = smem + C::MAIN_B;                    // [16][D] bf16, swizzled
     __nv_bfloat16* s_knew = reinterpret_cast<__nv_bfloat16*>(s_q + C::Q_B);   // [D] rotated new key
     __nv_bfloat16* s_vnew = s_knew + D;                                       // [D] new value
-    int* s_flag = reinterpret_cast<int*>(s_q + C::Q_B + C::NEW_B);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int split = blockIdx.x, S = gridDim.x;
-    const int kvh = blockIdx.y / p.ngroups, grp = blockIdx.y - kvh * p.ngroups;
-    const int b = blockIdx.z;
+    const int kvh = pc.kvh, grp = pc.grp, b = pc.b;
     const int g0 = grp * p.gpg;
     const int gcount = min(p.gpg, p.G - g0);
     const int hq0 = kvh * p.G + g0;
     const bool has_new = p.k_new != nullptr;
 
-    const int pos = __ldg(p.seqlens + b);
-    const int seqlen_k = pos + (has_new ? 1 : 0);
-    const int n_chunks = (seqlen_k + C::CH - 1) / C::CH;
-    const int cps = (n_chunks + S - 1) / S;
-    const int c0 = split * cps;
-    const int c1 = min(n_chunks, c0 + cps);
+    const int pos = pc.pos;
+    const int seqlen_k = pc.seqlen_k;
+    const int n_chunks = pc.n_chunks;
+    const int c0 = pc.c0;
+    const int c1 = pc.c1;
     const int n_iters = max(0, c1 - c0);
-    const bool owns_new = has_new && n_iters > 0 && (c1 == n_chunks);   // this CTA streams the chunk holding `pos`
+    const bool owns_new = has_new && n_iters > 0 && (c1 == n_chunks);   // this piece streams the chunk holding `pos`
 
     const int32_t* bt = p.block_table + (int64_t)b * p.bt_sb;
     uint8_t* my_kv = s_kv + warp * (STAGES * C::STAGE_B);
@@ -168,7 +173,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     // Programmatic dependent launch: everything above only read state that the caller
     // guarantees is older than the preceding kernel in the stream (lengths, block table, cached
     // pages); q / k_new / v_new, the workspace and every global write come after the wait.
-    if (p.pdl) {
+    if (pdl && p.pdl) {
         if (p.pdl == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         asm volatile("griddepcontrol.wait;" ::: "memory");
     }
@@ -346,7 +351,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     cp_async_wait<0>();
     // late trigger: the next kernel's CTAs may take over SMs from here on (their KV prefetch
     // overlaps this kernel's merge epilogue and tail)
-    if (p.pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (pdl && p.pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();                                    // ring buffers are dead -> reuse as merge scratch
 
     // ---- merge the warps of this CTA
@@ -368,7 +373,6 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     }
     __syncthreads();
 
-    const int64_t bh0 = (int64_t)b * p.Hq + hq0;
     for (int idx = tid; idx < gcount * D; idx += C::THREADS) {
         const int g = idx / D, d = idx - g * D;
         float M = -CUDART_INF_F;
@@ -384,6 +388,34 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
         }
         const float val = (L > 0.0f) ? acc / L : 0.0f;
         const float lse = (L > 0.0f) ? (M * p.scale + __logf(L)) : -CUDART_INF_F;
+        sink(g, d, val, lse);
+    }
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, C::MINB)
+paged_decode_kernel(const __grid_constant__ DecodeParams p) {
+    constexpr int D = C::D;
+    extern __shared__ __align__(128) uint8_t smem[];
+    int* s_flag = reinterpret_cast<int*>(smem + C::MAIN_B + C::Q_B + C::NEW_B);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int split = blockIdx.x, S = gridDim.x;
+    Piece pc;
+    pc.kvh = blockIdx.y / p.ngroups; pc.grp = blockIdx.y - pc.kvh * p.ngroups;
+    pc.b = blockIdx.z;
+    const int b = pc.b;
+    const int g0 = pc.grp * p.gpg;
+    const int gcount = min(p.gpg, p.G - g0);
+    const int hq0 = pc.kvh * p.G + g0;
+    pc.pos = __ldg(p.seqlens + b);
+    pc.seqlen_k = pc.pos + (p.k_new != nullptr ? 1 : 0);
+    pc.n_chunks = (pc.seqlen_k + C::CH - 1) / C::CH;
+    const int cps = (pc.n_chunks + S - 1) / S;
+    pc.c0 = split * cps;
+    pc.c1 = min(pc.n_chunks, pc.c0 + cps);
+    const int64_t bh0 = (int64_t)b * p.Hq + hq0;
+
+    decode_piece<C>(p, smem, pc, true, [&](int g, int d, float val, float lse) {
         if (S == 1) {
             p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(val);
             if (d == 0 && p.lse_out) p.lse_out[bh0 + g] = lse;
@@ -391,7 +423,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
             p.ws_o[((bh0 + g) * S + split) * D + d] = val;
             if (d == 0) p.ws_lse[(bh0 + g) * S + split] = lse;
         }
-    }
+    });
     if (S == 1) return;
 
     // ---- split merge by the last-arriving CTA of this (b, kv head, group)
@@ -439,6 +471,147 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
             if (w != 0.0f) acc += w * __ldcg(po + (int64_t)s * D);
         }
         p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(acc);
+    }
+}
+
+// ------------------------------------------------------------------ balanced persistent form
+// Stream-K style scheduling for ragged / small batches: the grid is a fixed number of CTAs
+// (#SMs x resident CTAs, independent of the lengths -> CUDA-graph safe) and the chunks of ALL
+// (sequence, kv head, group) segments, laid end to end, are cut into equal shares, one per CTA.
+// A share may cover the tail of one segment, whole segments, and the head of another; whole
+// segments are written directly, the (at most two) partial pieces of a CTA go to workspace slots
+// 2*cta + {0: piece starts at the CTA's range start, 1: otherwise} and the last CTA to arrive on
+// the segment's counter merges them.  Every CTA derives the schedule from cache_seqlens itself.
+constexpr int kSkMaxB = 512;         // prefix table of chunk counts lives in shared memory
+constexpr int kSkMinChunks = 4;      // never cut shares below 4 chunks (256 tokens at CH = 64)
+constexpr int kSkMaxCtas = 1024;     // workspace slots = 2 per CTA
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, C::MINB)
+paged_decode_sk_kernel(const __grid_constant__ DecodeParams p) {
+    constexpr int D = C::D;
+    extern __shared__ __align__(128) uint8_t smem[];
+    int* s_flag = reinterpret_cast<int*>(smem + C::MAIN_B + C::Q_B + C::NEW_B);
+    int* s_pre = reinterpret_cast<int*>(smem + C::SMEM);          // [B + 1] exclusive prefix of chunk counts
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int B = p.B;
+    const int add_new = p.k_new != nullptr ? 1 : 0;
+
+    for (int i = tid; i < B; i += C::THREADS) {
+        const int len = __ldg(p.seqlens + i) + add_new;
+        s_pre[i + 1] = max(1, (len + C::CH - 1) / C::CH);         // an empty sequence still owns one (masked) chunk
+    }
+    if (tid == 0) s_pre[0] = 0;
+    __syncthreads();
+    if (warp == 0) {                                               // inclusive scan, 32 entries per step
+        int carry = 0;
+        for (int base = 1; base <= B; base += 32) {
+            const int i = base + lane;
+            int v = (i <= B) ? s_pre[i] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += t;
+            }
+            v += carry;
+            if (i <= B) s_pre[i] = v;
+            carry = __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+
+    const int Y = p.Hkv * p.ngroups;
+    const int Wt = Y * s_pre[B];
+    const int P = gridDim.x;
+    const int q = max(kSkMinChunks, (Wt + P - 1) / P);
+    int gpos = blockIdx.x * q;
+    const int gend = min(Wt, gpos + q);
+
+    while (gpos < gend) {
+        int lo = 0, hi = B - 1;                                    // largest b with Y * pre[b] <= gpos
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (Y * s_pre[mid] <= gpos) lo = mid; else hi = mid - 1;
+        }
+        const int b = lo;
+        const int n_b = s_pre[b + 1] - s_pre[b];
+        const int rem = gpos - Y * s_pre[b];
+        const int y = rem / n_b;
+        const int cs = rem - y * n_b;
+        const int ce = min(n_b, cs + (gend - gpos));
+        const int seg0 = gpos - cs;                                // global chunk coordinate of the segment start
+        const int c_first = seg0 / q, c_last = (seg0 + n_b - 1) / q;
+        const int npieces = c_last - c_first + 1;
+        const bool whole = npieces == 1;
+        const int slot = 2 * blockIdx.x + ((seg0 <= (int)blockIdx.x * q) ? 0 : 1);
+
+        Piece pc;
+        pc.b = b; pc.kvh = y / p.ngroups; pc.grp = y - pc.kvh * p.ngroups;
+        pc.c0 = cs; pc.c1 = ce; pc.n_chunks = n_b;
+        pc.pos = __ldg(p.seqlens + b);
+        pc.seqlen_k = pc.pos + add_new;
+        const int g0 = pc.grp * p.gpg;
+        const int gcount = min(p.gpg, p.G - g0);
+        const int hq0 = pc.kvh * p.G + g0;
+        const int64_t bh0 = (int64_t)b * p.Hq + hq0;
+
+        decode_piece<C>(p, smem, pc, false, [&](int g, int d, float val, float lse) {
+            if (whole) {
+                p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(val);
+                if (d == 0 && p.lse_out) p.lse_out[bh0 + g] = lse;
+            } else {
+                p.ws_o[((int64_t)slot * 16 + g) * D + d] = val;
+                if (d == 0) p.ws_lse[slot * 16 + g] = lse;
+            }
+        });
+
+        if (!whole) {
+            __syncthreads();
+            if (tid == 0) {
+                int32_t* ctr = p.counters + ((int64_t)b * Y + y);
+                int prev;
+                asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(prev) : "l"(ctr) : "memory");
+                const int last = (prev == npieces - 1);
+                if (last) *ctr = 0;
+                *s_flag = last;
+            }
+            __syncthreads();
+            if (*s_flag) {
+                // slot of piece i of this segment: CTA c_first + i; only the first piece can be a CTA's second slot
+                auto slot_of = [&](int i) { return 2 * (c_first + i) + ((i == 0 && seg0 > c_first * q) ? 1 : 0); };
+                float* c_w = reinterpret_cast<float*>(smem);       // [gcount][npieces] merge weights
+                for (int idx = tid; idx < gcount * npieces; idx += C::THREADS) {
+                    const int g = idx / npieces, i = idx - g * npieces;
+                    c_w[idx] = __ldcg(p.ws_lse + slot_of(i) * 16 + g);
+                }
+                __syncthreads();
+                for (int g = warp; g < gcount; g += C::NWARPS) {
+                    float mx = -CUDART_INF_F;
+                    for (int i = lane; i < npieces; i += 32) mx = fmaxf(mx, c_w[g * npieces + i]);
+#pragma unroll
+                    for (int o2 = 16; o2 > 0; o2 >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o2));
+                    const float mref = (mx == -CUDART_INF_F) ? 0.0f : mx;
+                    float sum = 0.0f;
+                    for (int i = lane; i < npieces; i += 32) sum += __expf(c_w[g * npieces + i] - mref);
+                    sum = warp_sum(sum);
+                    const float inv = (sum > 0.0f) ? 1.0f / sum : 0.0f;
+                    for (int i = lane; i < npieces; i += 32) c_w[g * npieces + i] = __expf(c_w[g * npieces + i] - mref) * inv;
+                    if (lane == 0 && p.lse_out) p.lse_out[bh0 + g] = (sum > 0.0f) ? (mref + __logf(sum)) : -CUDART_INF_F;
+                }
+                __syncthreads();
+                for (int idx = tid; idx < gcount * D; idx += C::THREADS) {
+                    const int g = idx / D, d = idx - g * D;
+                    float acc = 0.0f;
+                    for (int i = 0; i < npieces; ++i) {
+                        const float w = c_w[g * npieces + i];
+                        if (w != 0.0f) acc += w * __ldcg(p.ws_o + ((int64_t)slot_of(i) * 16 + g) * D + d);
+                    }
+                    p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(acc);
+                }
+            }
+        }
+        __syncthreads();                                           // shared memory is reused by the next piece
+        gpos += ce - cs;
     }
 }
 
@@ -494,6 +667,37 @@ static WsLayout ws_layout(int B, int Hq, int D, int S) {
     return w;
 }
 
+// balanced form: [ arrival counters (same fixed region) | lse partials [2 * ctas][16] | O partials [2 * ctas][16][D] ]
+static WsLayout ws_layout_sk(int D) {
+    WsLayout w;
+    w.counters_off = 0;
+    w.lse_off = kMaxCounters * 4;
+    w.o_off = w.lse_off + (int64_t)2 * kSkMaxCtas * 16 * 4;
+    w.total = w.o_off + (int64_t)2 * kSkMaxCtas * 16 * D * 4;
+    return w;
+}
+
+template <class C>
+static int launch_decode_sk(const DecodeParams& p, cudaStream_t st) {
+    static bool attr_done = false;
+    static int attr_dev = -1, n_sm = 0;
+    const int smem_bytes = C::SMEM + (int)align_up((int64_t)(p.B + 1) * 4, 16);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done || attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(paged_decode_sk_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             C::SMEM + (kSkMaxB + 4) * 4);
+        if (e != cudaSuccess) { set_error("decode: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
+        if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm <= 0) n_sm = 148;
+        attr_done = true; attr_dev = dev;
+    }
+    int ctas = n_sm * C::MINB;
+    if (ctas > kSkMaxCtas) ctas = kSkMaxCtas;
+    paged_decode_sk_kernel<C><<<ctas, C::THREADS, smem_bytes, st>>>(p);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
 template <class C>
 static int launch_decode(const DecodeParams& p, int S, cudaStream_t st) {
     static bool attr_done = false;      // per instantiation; the attribute is per-function, per-context
@@ -531,6 +735,11 @@ extern "C" int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hk
     return ws_layout(B, Hq, D, num_splits).total;
 }
 
+extern "C" int64_t b200_decode_balanced_workspace_bytes(int32_t D) {
+    if (D <= 0) return -1;
+    return ws_layout_sk(D).total;
+}
+
 extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     if (!a) B200_FAIL(B200_E_NULL, "decode: null args");
     if (!a->q || !a->k_cache || !a->v_cache || !a->cache_seqlens || !a->block_table || !a->out)
@@ -561,7 +770,20 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     const int ngroups = (G + 15) / 16;
     const int S = a->num_splits;
     DecodeParams p;
-    if (S > 1) {
+    const bool balanced = (a->flags & B200_DECODE_FLAG_BALANCED) != 0;
+    if (balanced) {
+        if (a->B > kSkMaxB) B200_FAIL(B200_E_RANGE, "decode: balanced scheduling supports B <= %d (got %d)", kSkMaxB, a->B);
+        if (a->flags & B200_DECODE_FLAG_PDL) B200_FAIL(B200_E_UNSUPPORTED, "decode: balanced scheduling has no PDL form");
+        if ((int64_t)a->B * a->Hkv * ngroups > kMaxCounters)
+            B200_FAIL(B200_E_RANGE, "decode: B * Hkv * groups exceeds the %lld split-merge counters", (long long)kMaxCounters);
+        const WsLayout w = ws_layout_sk(a->D);
+        if (!a->workspace || a->workspace_bytes < w.total)
+            B200_FAIL(B200_E_RANGE, "decode: workspace %lld B < required %lld B", (long long)a->workspace_bytes, (long long)w.total);
+        uint8_t* ws = (uint8_t*)a->workspace;
+        p.counters = (int32_t*)(ws + w.counters_off);
+        p.ws_lse = (float*)(ws + w.lse_off);
+        p.ws_o = (float*)(ws + w.o_off);
+    } else if (S > 1) {
         if ((int64_t)a->B * a->Hkv * ngroups > kMaxCounters)
             B200_FAIL(B200_E_RANGE, "decode: B * Hkv * groups = %lld exceeds the %lld split-merge counters",
                       (long long)a->B * a->Hkv * ngroups, (long long)kMaxCounters);
@@ -595,6 +817,24 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
     cudaStream_t st = (cudaStream_t)stream;
 
+    if (balanced) {
+        if (a->D == 128) {
+            switch (a->variant) {
+                case 0:
+                case 6: return launch_decode_sk<DCfg<128, 4, 16, 2, 3>>(p, st);
+                case 1: return launch_decode_sk<DCfg<128, 4, 16, 3, 2>>(p, st);
+                case 5: return launch_decode_sk<DCfg<128, 2, 16, 4, 3>>(p, st);
+                case 8: return launch_decode_sk<DCfg<128, 2, 32, 3, 2>>(p, st);
+                default: B200_FAIL(B200_E_RANGE, "decode: variant %d has no balanced form", a->variant);
+            }
+        }
+        switch (a->variant) {
+            case 0:
+            case 1: return launch_decode_sk<DCfg<64, 4, 32, 3, 2>>(p, st);
+            case 2: return launch_decode_sk<DCfg<64, 4, 16, 4, 3>>(p, st);
+            default: B200_FAIL(B200_E_RANGE, "decode: variant %d has no balanced form", a->variant);
+        }
+    }
     if (a->D == 128) {
         switch (a->variant) {
             case 1: return launch_decode<DCfg<128, 4, 16, 3, 2>>(p, S, st);   //  96 KB, 2 CTA/SM

@@ -16,7 +16,7 @@ from _cases import assert_close, make_paged_case, to_dev
 pytestmark = pytest.mark.gpu
 
 
-def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rotary=True):
+def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rotary=True, balanced=None):
     d = to_dev(case)
     kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
     want = paged_attention_oracle(case["q"], kc_ref, vc_ref,
@@ -28,7 +28,7 @@ def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rota
         d["k"][:, 0] if append else None, d["v"][:, 0] if append else None,
         d["cos"] if rotary else None, d["sin"] if rotary else None,
         d["seqlens"], d["table"], softmax_scale=case["scale"], rotary_interleaved=interleaved,
-        num_splits=num_splits, variant=variant)
+        num_splits=num_splits, variant=variant, balanced=balanced)
     torch.cuda.synchronize()
     return got, want[:, 0], d, kc_ref, vc_ref
 
@@ -71,6 +71,80 @@ def test_all_kernel_variants(D, variants):
     for v in variants:
         case = make_paged_case(8, Hq, Hkv, D, lens, seed=10 + v)
         check(case, variant=v, num_splits=3)
+
+
+# ---------------------------------------------------------------- balanced (persistent stream-K) scheduling
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (8, 1, 128), (28, 4, 128), (64, 8, 128), (14, 2, 64), (32, 1, 64)])
+def test_balanced_edge_lengths(Hq, Hkv, D):
+    """Same oracle, fixed persistent grid: shares cross sequence / head boundaries, so every piece
+    position (head of a segment, tail, whole, single-chunk, empty sequence) occurs."""
+    case = make_paged_case(len(LENS_EDGE), Hq, Hkv, D, LENS_EDGE, seed=Hq + D)
+    check(case, balanced=True)
+    check(make_paged_case(len(LENS_EDGE), Hq, Hkv, D, LENS_EDGE, seed=Hq + D + 1), balanced=True, interleaved=True)
+
+
+@pytest.mark.parametrize("lens", [
+    [8191] * 3, [4095] * 32, [32767, 5, 130, 2000, 64, 63, 12000, 1], [0], [100000], [255, 256] * 20,
+    [int(128 * (256 ** (i / 63.0))) for i in range(64)],            # log-uniform 128 .. 32768 (configs[2])
+])
+def test_balanced_ragged_batches(lens):
+    Hq, Hkv, D = 28, 4, 128
+    case = make_paged_case(len(lens), Hq, Hkv, D, lens, seed=len(lens) + lens[0] % 97, rot_rows=max(lens) + 8)
+    check(case, balanced=True)
+
+
+@pytest.mark.parametrize("variant,D", [(1, 128), (5, 128), (6, 128), (8, 128), (1, 64), (2, 64)])
+def test_balanced_variants(variant, D):
+    Hq, Hkv = (32, 8) if D == 128 else (14, 2)
+    lens = [700, 255, 256, 31, 4000, 1, 0, 513, 9000]
+    check(make_paged_case(len(lens), Hq, Hkv, D, lens, seed=20 + variant, rot_rows=9100), balanced=True, variant=variant)
+
+
+def test_balanced_matches_split_grid_and_shares_workspace():
+    """Both schedules on the same inputs (the merge order differs, so compare through the tolerance),
+    interleaved launches of both forms reuse one workspace (counters must come back to zero), and
+    the balanced form is graph-replay safe with lengths that change between replays."""
+    lens = [3000, 17, 900, 4095, 2048, 2049]
+    case = make_paged_case(len(lens), 32, 8, 128, lens, seed=77)
+    a = check(case, balanced=True)
+    b = check(case, num_splits=5)
+    c = check(case, balanced=True)
+    assert torch.equal(a, c)
+    assert (a.float() - b.float()).abs().max().item() < 2e-2
+    d = to_dev(case)
+    out = torch.empty(len(lens), 32, 128, dtype=torch.bfloat16, device="cuda")
+    args = (d["q"][:, 0], d["k_cache"], d["v_cache"], d["k"][:, 0], d["v"][:, 0], d["cos"], d["sin"], d["seqlens"],
+            d["table"])
+    b200ops.paged_attn_decode(*args, softmax_scale=case["scale"], out=out, balanced=True)       # warm-up (workspace)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        b200ops.paged_attn_decode(*args, softmax_scale=case["scale"], out=out, balanced=True)
+    for new_lens in ([10, 11, 12, 13, 14, 15], [4000, 1, 1, 1, 1, 1], lens):
+        c2 = make_paged_case(len(lens), 32, 8, 128, new_lens, seed=77)
+        c2["table"] = case["table"]                         # same pages: only the lengths move
+        for k in ("k_cache", "v_cache"):
+            d[k].copy_(case[k])
+        d["seqlens"].copy_(torch.tensor(new_lens, dtype=torch.int32))
+        g.replay()
+        torch.cuda.synchronize()
+        kc, vc = case["k_cache"].clone(), case["v_cache"].clone()
+        want = paged_attention_oracle(case["q"], kc, vc, case["k"], case["v"], case["cos"], case["sin"],
+                                      torch.tensor(new_lens, dtype=torch.int32), case["table"], case["scale"], True, False)
+        assert_close(out, want[:, 0], what=f"graph replay lens={new_lens}")
+        assert torch.equal(d["v_cache"].cpu(), vc)
+
+
+def test_balanced_lse_output():
+    lens = [513, 64, 3000]
+    case = make_paged_case(3, 32, 8, 128, lens, seed=5)
+    d = to_dev(case)
+    lse = torch.empty(3, 32, dtype=torch.float32, device="cuda")
+    lse2 = torch.empty_like(lse)
+    args = (d["q"][:, 0], d["k_cache"], d["v_cache"], None, None, None, None, d["seqlens"], d["table"])
+    b200ops.paged_attn_decode(*args, softmax_scale=case["scale"], softmax_lse=lse, balanced=True)
+    b200ops.paged_attn_decode(*args, softmax_scale=case["scale"], softmax_lse=lse2, num_splits=1)
+    assert torch.allclose(lse, lse2, atol=2e-3, rtol=1e-4)
 
 
 def test_workspace_survives_shape_changes():

@@ -88,6 +88,11 @@ def main():
     if rank == 0:
         print(json.dumps(res), flush=True)
     ok = same and rel0 < 0.02 and err == 0
+    # graphs that captured NCCL kernels must be gone before the communicator is destroyed (else destroy waits forever)
+    del runner, mgr
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)

@@ -24,6 +24,10 @@ SHAPES = {
     "q05": dict(B=1, Hq=14, Hkv=2, D=64, ctx=192),
     "l8b1": dict(B=1, Hq=32, Hkv=8, D=128, ctx=4096),
     "l8b8": dict(B=8, Hq=32, Hkv=8, D=128, ctx=4096),
+    "l8b16": dict(B=16, Hq=32, Hkv=8, D=128, ctx=4096),
+    # configs[2]: 64 ragged sequences, context lengths log-uniform on [128, 32768]
+    "q7ragged": dict(B=64, Hq=28, Hkv=4, D=128, ctx=32768, ragged=True),
+    "l8ragged": dict(B=32, Hq=32, Hkv=8, D=128, ctx=16384, ragged=True),
 }
 
 
@@ -35,27 +39,41 @@ def main():
     ap.add_argument("--iters", type=int, default=40)
     ap.add_argument("--no-fa", action="store_true")
     ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--tag", default="")
     args = ap.parse_args()
     sh = SHAPES[args.shape]
     B, Hq, Hkv, D, ctx = (sh[k] for k in ("B", "Hq", "Hkv", "D", "ctx"))
     page = 256
     per_seq = ctx // page
     dev = torch.device("cuda")
-    kv_bytes = B * ctx * Hkv * D * 2 * 2
+    if sh.get("ragged"):
+        gl = torch.Generator().manual_seed(0)
+        u = torch.rand(B, generator=gl)
+        lens_list = [int(128 * (ctx / 128) ** float(x)) for x in u]          # log-uniform on [128, ctx]
+    else:
+        lens_list = [ctx] * B
+    kv_bytes = sum(lens_list) * Hkv * D * 2 * 2
     n_sets = max(2, min(8, int(1.5e9 // kv_bytes) + 1))            # rotate caches so L2 never helps
-    n_blocks = B * per_seq + 4
+    need = [-(-n // page) for n in lens_list]
+    n_blocks = sum(need) + 4
     g = torch.Generator().manual_seed(0)
     caches = [(torch.randn(n_blocks, page, Hkv, D, device=dev, dtype=torch.bfloat16),
                torch.randn(n_blocks, page, Hkv, D, device=dev, dtype=torch.bfloat16)) for _ in range(n_sets)]
-    table = torch.randperm(n_blocks, generator=g)[: B * per_seq].view(B, per_seq).to(torch.int32).to(dev)
-    lens = torch.full((B,), ctx - 1, dtype=torch.int32, device=dev)
+    perm = torch.randperm(n_blocks, generator=g).tolist()
+    table = torch.full((B, per_seq), -1, dtype=torch.int32)
+    it = iter(perm)
+    for b in range(B):
+        for j in range(need[b]):
+            table[b, j] = next(it)
+    table = table.to(dev)
+    lens = torch.tensor([n - 1 for n in lens_list], dtype=torch.int32, device=dev)
     q = torch.randn(B, Hq, D, device=dev, dtype=torch.bfloat16)
     k = torch.randn(B, Hkv, D, device=dev, dtype=torch.bfloat16)
     v = torch.randn(B, Hkv, D, device=dev, dtype=torch.bfloat16)
     cos, sin = build_rotary_tables(D, max(8192, ctx + 1))
     cos, sin = cos[:, : D // 2].contiguous().to(dev), sin[:, : D // 2].contiguous().to(dev)
     out = torch.empty(B, Hq, D, device=dev, dtype=torch.bfloat16)
-    nbytes = decode_algorithmic_bytes([ctx] * B, Hq, Hkv, D, page)
+    nbytes = decode_algorithmic_bytes(lens_list, Hq, Hkv, D, page)
 
     def timeit(fn, iters=args.iters):
         for i in range(3):
@@ -99,7 +117,11 @@ def main():
         for S in [int(x) for x in args.splits.split(",")]:
             def fn(i, var=var, S=S):
                 kc, vc = caches[i % n_sets]
-                b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, num_splits=S, variant=var, out=out, pdl=args.pdl)
+                if S == 0:          # 0 = balanced persistent (stream-K) schedule
+                    b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, variant=var, out=out, balanced=True)
+                else:
+                    b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, num_splits=S, variant=var, out=out,
+                                              pdl=args.pdl, balanced=False)
             try:
                 us = timeit_graph(fn)
             except Exception as e:  # noqa: BLE001
@@ -126,7 +148,7 @@ def main():
     best = min(results, key=lambda r: r["us"]) if results else None
     print("best:", best)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", f"tune_{args.shape}{'_pdl%d' % args.pdl if args.pdl else ''}.json"), "w") as f:
+    with open(os.path.join(ROOT, "gpurun_out", f"tune_{args.shape}{'_pdl%d' % args.pdl if args.pdl else ''}{args.tag}.json"), "w") as f:
         json.dump(dict(shape=sh, algorithmic_bytes=nbytes, results=results, flash_attn=fa, best=best,
                        gpu=torch.cuda.get_device_name(0)), f, indent=1)
 
