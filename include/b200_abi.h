@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 6
+#define B200_ABI_VERSION 7
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -257,7 +257,7 @@ int b200_paged_attn_prefill(const b200_prefill_args* args, void* stream);
  *   - CONSECUTIVE calls must read x from DIFFERENT buffers (two alternating
  *     slots): the barrier of call k+1 is what tells a rank that its peers
  *     finished reading the buffer of call k;
- *   - flags: uint32 [B200_AR_MAX_CTAS][B200_AR_MAX_WORLD] per rank, zeroed
+ *   - flags: uint32 [B200_AR_MAX_CTAS][B200_AR_MAX_WORLD] (+ [B200_AR_MAX_CTAS], row-sharded form) per rank, zeroed
  *     once; epoch: LOCAL uint32 [B200_AR_MAX_CTAS + 1], zeroed once; word
  *     [B200_AR_MAX_CTAS] is set to 1 if a wait timed out (peer missing).
  * ------------------------------------------------------------------------ */
@@ -279,7 +279,21 @@ typedef struct b200_ar_args {
     int32_t rank, world;      /* world in {1, 2, 4, 8}                             */
     int32_t ss_rounded;       /* see above                                         */
     int32_t timeout_ms;       /* flag wait bound; 0 = default 2000                 */
+    int32_t mode;             /* 0 = one-shot, or B200_AR_MODE_ROW_SHARDED         */
+    void*   y_peers[B200_AR_MAX_WORLD];  /* row-sharded: rank r's y buffer (entry `rank` == y) */
 } b200_ar_args;
+
+/* Row-sharded ("two-shot") form for world > 1, rows <= B200_AR_MAX_CTAS: rank r OWNS rows
+ * [r*ceil(rows/world), ...).  The owner of a row waits for every peer's per-row "ready" flag, loads the
+ * row from all ranks, reduces, adds ITS residual row, normalises, and stores y into EVERY rank's y
+ * buffer (peer stores over NVLink), then raises the row's "done" flag on every rank.  Each rank moves
+ * (world-1)/world of one activation in each direction instead of (world-1) activations inbound.
+ * Contract differences: `residual` is read and `res_out` written ONLY for owned rows (the residual
+ * stream stays row-sharded across calls — what the decode loop needs); y must live in peer-visible
+ * memory; flags: a second array u32 [B200_AR_MAX_CTAS] follows the first in every rank's flag region
+ * (total (B200_AR_MAX_WORLD + 1) * B200_AR_MAX_CTAS words); consecutive calls need NOT alternate
+ * buffers (the done flag is the proof that the owner finished reading). */
+#define B200_AR_MODE_ROW_SHARDED 1
 
 int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
 

@@ -7,13 +7,14 @@ elementwise kernels that follow it at core/layer/model_graph.py:210-216 and :219
 One process per GPU.  Every rank cudaMalloc's ONE slab (IPC-exportable, outside torch's caching
 allocator), laid out as
 
-    [ flags  u32[1024][8] | epoch u32[1025] (local only) | pad | slot 0 | slot 1 ]
+    [ flags u32[1024][8] + u32[1024] | epoch u32[1025] (local only) | pad | slot 0 | slot 1 | y ]
 
 exports it with cudaIpcGetMemHandle, exchanges the 64-byte handles through torch.distributed
 (plumbing only) and maps every peer's slab.  The two data slots are the GEMM output buffers the
 kernel reads on every rank; consecutive calls must alternate slots (the barrier of call k+1 proves
 that all peers finished reading the slot of call k), which :meth:`allreduce_residual_rmsnorm`
-enforces on the host at call / capture time.
+enforces on the host at call / capture time.  ``y`` is the peer-visible output buffer of the
+row-sharded form, in which the owner of a row pushes the normalised row to every rank.
 """
 from __future__ import annotations
 
@@ -25,7 +26,7 @@ import torch
 from . import _lib
 from ._lib import ArArgs, check, lib
 
-_FLAG_BYTES = _lib.AR_MAX_CTAS * _lib.AR_MAX_WORLD * 4
+_FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4        # ready flags [1024][8] + done flags [1024]
 _EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 1) * 4 + 255) // 256 * 256
 _HEADER = _FLAG_BYTES + _EPOCH_BYTES
 
@@ -96,7 +97,7 @@ class PeerComm:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.slot_bytes = (int(slot_bytes) + 255) // 256 * 256
         self.timeout_ms = int(timeout_ms)
-        total = _HEADER + 2 * self.slot_bytes
+        total = _HEADER + 3 * self.slot_bytes
         with torch.cuda.device(self.device):
             p = C.c_void_p()
             check(lib.b200_comm_alloc(total, C.byref(p)), "b200_comm_alloc")
@@ -130,6 +131,13 @@ class PeerComm:
         off = _HEADER + idx * self.slot_bytes
         return self._bytes[off: off + rows * n * 2].view(torch.bfloat16).view(rows, n)
 
+    def ybuf(self, rows: int, n: int) -> torch.Tensor:
+        """bf16 [rows, n] view of the local peer-visible y buffer (row-sharded form: every owner
+        pushes its normalised rows into every rank's copy)."""
+        assert rows * n * 2 <= self.slot_bytes, "PeerComm y buffer too small"
+        off = _HEADER + 2 * self.slot_bytes
+        return self._bytes[off: off + rows * n * 2].view(torch.bfloat16).view(rows, n)
+
     def fits(self, rows: int, n: int) -> bool:
         return rows * n * 2 <= self.slot_bytes and n % 8 == 0 and n <= 16384
 
@@ -141,10 +149,14 @@ class PeerComm:
     # ------------------------------------------------------------------ the fused op
     def allreduce_residual_rmsnorm(self, slot_idx: int, rows: int, n: int, residual: Optional[torch.Tensor],
                                    weight: Optional[torch.Tensor], y: Optional[torch.Tensor],
-                                   res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False):
+                                   res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False,
+                                   sharded: bool = False):
         """res_out = bf16(bf16(sum over ranks of slot[slot_idx][:rows, :n]) + residual);
-        y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable."""
-        if slot_idx == self._last_slot:
+        y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable.
+        ``sharded``: the row-sharded form (B200_AR_MODE_ROW_SHARDED) — ``y`` must be a prefix view of
+        :meth:`ybuf`, rows <= 1024, and ``residual`` / ``res_out`` are only read / written for the rows
+        this rank owns."""
+        if slot_idx == self._last_slot and not sharded:
             raise AssertionError("PeerComm: consecutive fused all-reduces must alternate slots 0 / 1")
         self._last_slot = slot_idx
         x = self.slot(slot_idx, rows, n)
@@ -156,6 +168,14 @@ class PeerComm:
         a.epoch = self._base + _FLAG_BYTES
         _fill_common(a, x, residual, weight, y, res_out, eps, ss_rounded)
         a.rank, a.world, a.timeout_ms = self.rank, self.world, self.timeout_ms
+        if sharded:
+            yoff = _HEADER + 2 * self.slot_bytes
+            assert y is not None and y.data_ptr() == self._base + yoff and y.stride(0) == n, \
+                "PeerComm: the row-sharded form writes y into ybuf() on every rank"
+            assert rows <= _lib.AR_MAX_CTAS
+            a.mode = _lib.AR_MODE_ROW_SHARDED
+            for r in range(self.world):
+                a.y_peers[r] = self._peer_base[r] + yoff
         check(lib.b200_allreduce_residual_rmsnorm(C.byref(a), torch.cuda.current_stream().cuda_stream),
               "b200_allreduce_residual_rmsnorm")
         return y, res_out

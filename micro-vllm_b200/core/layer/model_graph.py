@@ -27,6 +27,7 @@ the hot path this repo owns:
 GEMMs stay ``torch.matmul(..., out=)`` (cuBLAS; out of scope).
 """
 import logging
+import os
 from typing import Dict, List
 
 import torch
@@ -126,9 +127,18 @@ class ModelGraphRunner:
         self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
         if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
             self._comm = None
+        # Row-sharded ("two-shot") reduction: each rank reduces + normalises only the rows it owns and pushes y to
+        # all ranks; the residual stream stays row-sharded, so it needs the final norm fused (ln_f is a kernel norm).
+        # B200_AR_SHARDED = 0 / 1 forces it; default: from 4 ranks up (at 2 ranks it moves the same bytes).
+        self._ar_sharded = False
         if self._comm is not None:
             self._attn_out = self._comm.slot(0, mb, self.hidden_dim)
             self._mlp_out = self._comm.slot(1, mb, self.hidden_dim)
+            want = os.environ.get("B200_AR_SHARDED", "auto")
+            fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False))
+            self._ar_sharded = fusable and mb <= 1024 and (want == "1" or (want == "auto" and self.world_size >= 4))
+            if self._ar_sharded:
+                self._normed = self._comm.ybuf(mb, self.hidden_dim)
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
 
     # ------------------------------------------------------------------ per-layer pieces
@@ -172,7 +182,8 @@ class ModelGraphRunner:
         eps = norm.eps if norm is not None else 0.0
         if self._comm is not None:
             self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
-                                                  y if norm is not None else None, res_out, eps, ss_rounded)
+                                                  y if norm is not None else None, res_out, eps, ss_rounded,
+                                                  sharded=self._ar_sharded)
         else:
             all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
             allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,

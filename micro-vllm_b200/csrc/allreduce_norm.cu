@@ -32,6 +32,8 @@ struct ArParams {
     float eps;
     int rank, ss_rounded;
     long long timeout_cycles;
+    __nv_bfloat16* yp[B200_AR_MAX_WORLD];   // row-sharded form: every rank's y buffer (entry `rank` is local)
+    int rows_per_rank;                      // row-sharded form: rank r owns rows [r * rows_per_rank, ...)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -67,7 +69,23 @@ template <> struct ArW<float> {
     }
 };
 
-template <int WS, int VPT, typename WT>
+// bounded wait for flag >= e (signed distance: the epoch may wrap)
+__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t e, const ArParams& p) {
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(flag) - e) < 0) {
+        if (clock64() - t0 > p.timeout_cycles) {              // a peer never arrived: flag it, do not hang the GPU
+            atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u);
+            break;
+        }
+    }
+}
+
+// TS = row-sharded ("two-shot") form: grid = rows; the CTA of row i on the rank that OWNS row i waits for
+// every peer's "x row ready" flag, reduces + normalises the row and pushes y to every rank, then raises
+// the row's "done" flag on every rank; the CTAs of row i on the other ranks only raise their ready flag
+// and wait for the done flag.  NVLink traffic per rank drops from (world-1) * rows * n to
+// (world-1) * rows/world * n in each direction, for one extra flag hop.
+template <int WS, int VPT, typename WT, bool TS>
 __global__ void __launch_bounds__(1024)
 allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
     __shared__ float red[32];
@@ -75,21 +93,28 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
     const int T = blockDim.x;
     const int nvec = (int)(p.n >> 3);
 
-    if (WS > 1) {
+    if (TS) {
+        const uint32_t e = p.epoch[bid] + 1u;
+        const int owner = bid / p.rows_per_rank;
+        uint32_t* ready = p.flags[owner] + bid * B200_AR_MAX_WORLD;                       // on the owner: [row][src rank]
+        if (owner != p.rank) {
+            if (threadIdx.x != 0) return;
+            st_release_sys(ready + p.rank, e);                                            // my partial sums of this row are written
+            wait_flag(p.flags[p.rank] + B200_AR_MAX_CTAS * B200_AR_MAX_WORLD + bid, e, p); // owner pushed y (and is done with my x)
+            p.epoch[bid] = e;
+            return;
+        }
+        if (threadIdx.x < WS && threadIdx.x != p.rank) wait_flag(ready + threadIdx.x, e, p);
+        __syncthreads();
+        if (threadIdx.x == 0) p.epoch[bid] = e;
+    } else if (WS > 1) {
         const uint32_t e = p.epoch[bid] + 1u;
         if (threadIdx.x < WS) {
             const int peer = threadIdx.x;
             // everything this rank's stream wrote before this kernel (the GEMM that produced x) is ordered
             // before the flag by the release; the peer's acquire + its CTA barrier orders its loads after it
             st_release_sys(p.flags[peer] + bid * B200_AR_MAX_WORLD + p.rank, e);
-            const uint32_t* mine = p.flags[p.rank] + bid * B200_AR_MAX_WORLD + peer;
-            const long long t0 = clock64();
-            while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-                if (clock64() - t0 > p.timeout_cycles) {          // a peer never arrived: flag it, do not hang the GPU
-                    atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u);
-                    break;
-                }
-            }
+            wait_flag(p.flags[p.rank] + bid * B200_AR_MAX_WORLD + peer, e, p);
         }
         __syncthreads();
         if (threadIdx.x == 0) p.epoch[bid] = e;
@@ -167,35 +192,55 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
-                st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
+                if (TS) {
+#pragma unroll
+                    for (int k = 0; k < WS; ++k)                                           // local + (world-1) remote stores
+                        *reinterpret_cast<uint4*>(p.yp[k] + row * p.sy + (int64_t)v * 8) = o;
+                } else {
+                    st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
+                }
             }
         }
     }
+    if (TS) {
+        __syncthreads();                                     // every thread's pushes are ordered before the release below
+        if (threadIdx.x < WS && threadIdx.x != p.rank)
+            st_release_sys(p.flags[threadIdx.x] + B200_AR_MAX_CTAS * B200_AR_MAX_WORLD + bid, p.epoch[bid]);
+    }
 }
 
-template <int WS, typename WT>
+template <int WS, typename WT, bool TS>
 static int launch_ar(const ArParams& p, cudaStream_t st) {
     const int64_t nvec = p.n / 8;
     const unsigned grid = (unsigned)(p.rows < B200_AR_MAX_CTAS ? p.rows : B200_AR_MAX_CTAS);
     if (nvec <= 1024) {
-        const int threads = (int)((nvec + 31) & ~31LL);
-        allreduce_residual_rmsnorm_kernel<WS, 1, WT><<<grid, threads, 0, st>>>(p);
+        int threads = (int)((nvec + 31) & ~31LL);
+        if (threads < 32 * ((WS + 31) / 32)) threads = 32;
+        allreduce_residual_rmsnorm_kernel<WS, 1, WT, TS><<<grid, threads, 0, st>>>(p);
     } else {
         int threads = (int)((nvec + 1) / 2);
         threads = (threads + 31) & ~31;
-        allreduce_residual_rmsnorm_kernel<WS, 2, WT><<<grid, threads, 0, st>>>(p);
+        allreduce_residual_rmsnorm_kernel<WS, 2, WT, TS><<<grid, threads, 0, st>>>(p);
     }
     B200_CHECK_LAUNCH();
     return 0;
 }
 
 template <typename WT>
-static int dispatch_ws(int world, const ArParams& p, cudaStream_t st) {
+static int dispatch_ws(int world, bool sharded, const ArParams& p, cudaStream_t st) {
+    if (sharded) {
+        switch (world) {
+            case 2: return launch_ar<2, WT, true>(p, st);
+            case 4: return launch_ar<4, WT, true>(p, st);
+            case 8: return launch_ar<8, WT, true>(p, st);
+        }
+        B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: row-sharded form needs world 2, 4 or 8 (got %d)", world);
+    }
     switch (world) {
-        case 1: return launch_ar<1, WT>(p, st);
-        case 2: return launch_ar<2, WT>(p, st);
-        case 4: return launch_ar<4, WT>(p, st);
-        case 8: return launch_ar<8, WT>(p, st);
+        case 1: return launch_ar<1, WT, false>(p, st);
+        case 2: return launch_ar<2, WT, false>(p, st);
+        case 4: return launch_ar<4, WT, false>(p, st);
+        case 8: return launch_ar<8, WT, false>(p, st);
     }
     B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: world=%d (1, 2, 4 or 8)", world);
 }
@@ -231,6 +276,22 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         B200_FAIL(B200_E_ALIGN, "allreduce_residual_rmsnorm: pointers must be 16-byte aligned");
     if (a->stride_x % 8 || a->stride_res % 8 || (a->residual && a->stride_r % 8) || (a->y && a->stride_y % 8))
         B200_FAIL(B200_E_ALIGN, "allreduce_residual_rmsnorm: row strides must be multiples of 8 elements");
+    const bool sharded = (a->mode & B200_AR_MODE_ROW_SHARDED) != 0;
+    if (sharded) {
+        if (a->world < 2) B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: row-sharded form needs world > 1");
+        if (a->rows > B200_AR_MAX_CTAS)
+            B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: row-sharded form handles at most %d rows (got %lld)",
+                      B200_AR_MAX_CTAS, (long long)a->rows);
+        if (!a->weight) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: row-sharded form needs the norm (weight, y_peers)");
+        for (int r = 0; r < a->world; ++r) {
+            if (!a->y_peers[r] || !aligned16(a->y_peers[r]))
+                B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: y_peers[%d] missing or unaligned", r);
+            p.yp[r] = (__nv_bfloat16*)a->y_peers[r];
+        }
+        if (a->y_peers[a->rank] != a->y) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: y_peers[rank] must be y");
+        p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
+        if (p.rows_per_rank < 1) p.rows_per_rank = 1;
+    }
     if (a->rows == 0) return 0;
     p.epoch = (uint32_t*)a->epoch;
     p.r = (const __nv_bfloat16*)a->residual;
@@ -243,8 +304,8 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
     const int ms = a->timeout_ms > 0 ? a->timeout_ms : 2000;
     p.timeout_cycles = (long long)ms * 2000000LL;          // ~2 GHz SM clock upper bound
     cudaStream_t st = (cudaStream_t)stream;
-    if (a->weight && a->w_dtype == B200_DT_F32) return dispatch_ws<float>(a->world, p, st);
-    if (!a->weight || a->w_dtype == B200_DT_BF16) return dispatch_ws<__nv_bfloat16>(a->world, p, st);
+    if (a->weight && a->w_dtype == B200_DT_F32) return dispatch_ws<float>(a->world, sharded, p, st);
+    if (!a->weight || a->w_dtype == B200_DT_BF16) return dispatch_ws<__nv_bfloat16>(a->world, sharded, p, st);
     B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
 }
 

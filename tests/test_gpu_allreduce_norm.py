@@ -125,6 +125,43 @@ def test_emulated_ranks_single_gpu(world, rows, n, wdt):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("rows,n", [(64, 8192), (5, 3584), (1, 896), (3, 16384), (1000, 512)])
+def test_row_sharded_emulated_single_gpu(world, rows, n):
+    """Row-sharded form, one 'rank' per launch with all flags pre-set: the launch must reduce +
+    normalise exactly the rows it owns, push them into EVERY rank's y buffer and leave the rest alone."""
+    from b200ops import _lib
+    parts, r, w = _inputs(rows, n, world, world * 77 + rows + n)
+    parts_dev = [p.cuda() for p in parts]
+    wy, wres = allreduce_residual_rmsnorm_oracle(parts, r, w, 1e-5, True)
+    R = -(-rows // world)
+    nflag = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1)
+    ys = [torch.full((rows, n), 7.0, dtype=torch.bfloat16, device="cuda") for _ in range(world)]
+    for rank in range(world):
+        flags = [torch.ones(nflag, dtype=torch.int32, device="cuda") for _ in range(world)]
+        epoch = torch.zeros(_lib.AR_MAX_CTAS + 1, dtype=torch.int32, device="cuda")
+        res = torch.full((rows, n), 5.0, dtype=torch.bfloat16, device="cuda")
+        a = _lib.ArArgs()
+        for k in range(world):
+            a.x_peers[k], a.flag_peers[k], a.y_peers[k] = parts_dev[k].data_ptr(), flags[k].data_ptr(), ys[k].data_ptr()
+        a.epoch = epoch.data_ptr()
+        rd, wd = r.cuda(), w.cuda()
+        a.residual, a.weight, a.y, a.res_out = rd.data_ptr(), wd.data_ptr(), ys[rank].data_ptr(), res.data_ptr()
+        a.rows, a.n = rows, n
+        a.stride_x = a.stride_r = a.stride_y = a.stride_res = n
+        a.eps, a.w_dtype, a.rank, a.world, a.ss_rounded = 1e-5, _lib.DT_BF16, rank, world, 1
+        a.mode = _lib.AR_MODE_ROW_SHARDED
+        _lib.check(_lib.lib.b200_allreduce_residual_rmsnorm(C.byref(a), torch.cuda.current_stream().cuda_stream), "ar")
+        torch.cuda.synchronize()
+        lo, hi = min(rows, rank * R), min(rows, (rank + 1) * R)
+        assert torch.equal(res[lo:hi].cpu(), wres[lo:hi])
+        assert res[:lo].eq(5.0).all() and res[hi:].eq(5.0).all()            # residual stream stays row-sharded
+        assert epoch[:rows].eq(1).all() and int(epoch[_lib.AR_MAX_CTAS]) == 0
+    for k in range(world):                                                   # after all 'ranks' ran: every copy is complete
+        _ulp_ok(ys[k], wy)
+    assert all(torch.equal(ys[0], y) for y in ys[1:])
+
+
 def test_flag_wait_is_bounded():
     """No peer ever signals: the kernel must come back (error word set), not hang the GPU."""
     from b200ops import _lib
@@ -214,6 +251,33 @@ def _peer_worker(rank, world, port, q):
             wy, wres = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, False)
             _, wh = allreduce_residual_rmsnorm_oracle(parts1, wres, None, 0.0, True)
             assert torch.equal(res.cpu(), wres) and torch.equal(h.cpu(), wh), f"replay {it}"
+        # row-sharded form: y lands in every rank's ybuf, residual / res_out only for owned rows; graph replay
+        yb = comm.ybuf(rows, n)
+        rs = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
+        ro = torch.zeros_like(rs)
+        lo, hi = rank * (rows // world), (rank + 1) * (rows // world)
+        g2 = torch.cuda.CUDAGraph()
+        comm.allreduce_residual_rmsnorm(0, rows, n, rs, w.to(dev), yb, ro, 1e-5, True, sharded=True)     # warm-up
+        torch.cuda.synchronize()
+        dist.barrier()
+        with torch.cuda.graph(g2):
+            comm.allreduce_residual_rmsnorm(0, rows, n, rs, w.to(dev), yb, ro, 1e-5, True, sharded=True)
+            comm.allreduce_residual_rmsnorm(0, rows, n, ro, w.to(dev), yb, rs, 1e-5, False, sharded=True)
+        for it in range(10):
+            parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
+            r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
+            xs[0].copy_(parts0[rank].to(dev))
+            rs.copy_(r.to(dev))
+            torch.cuda.synchronize()
+            dist.barrier()
+            g2.replay()
+            torch.cuda.synchronize()
+            dist.barrier()
+            wy1, wres1 = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, True)
+            wy2, wres2 = allreduce_residual_rmsnorm_oracle(parts0, wres1, w, 1e-5, False)
+            assert torch.equal(ro[lo:hi].cpu(), wres1[lo:hi]) and torch.equal(rs[lo:hi].cpu(), wres2[lo:hi]), f"sharded replay {it}"
+            assert int(bf16_ulp_diff(yb.cpu(), wy2).max()) <= 1
+        del g2
         assert comm.error_flag() == 0
         with pytest.raises(AssertionError):                          # same slot twice in a row is refused on the host
             comm._last_slot = 1
