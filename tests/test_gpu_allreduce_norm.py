@@ -214,6 +214,7 @@ def _peer_worker(rank, world, port, q):
         assert comm is not None and comm.world == world
         g = torch.Generator().manual_seed(100)                       # same stream of numbers on every rank
         w = (1 + 0.2 * torch.randn(n, generator=g)).to(torch.bfloat16)
+        wd = w.to(dev)                                               # no host->device copies inside graph capture
         y = torch.empty(rows, n, dtype=torch.bfloat16, device=dev)
         res = torch.empty_like(y)
         for it in range(6):
@@ -222,7 +223,7 @@ def _peer_worker(rank, world, port, q):
             bs = [64, 1, 17, 32, 64, 5][it]
             slot = it % 2
             comm.slot(slot, rows, n)[:bs].copy_(parts[rank][:bs].to(dev))
-            comm.allreduce_residual_rmsnorm(slot, bs, n, r[:bs].to(dev), w.to(dev), y[:bs], res[:bs], 1e-5, bool(it & 1))
+            comm.allreduce_residual_rmsnorm(slot, bs, n, r[:bs].to(dev), wd, y[:bs], res[:bs], 1e-5, bool(it & 1))
             wy, wres = allreduce_residual_rmsnorm_oracle([p[:bs] for p in parts], r[:bs], w, 1e-5, bool(it & 1))
             assert torch.equal(res[:bs].cpu(), wres), f"iteration {it}: reduced residual differs"
             d = bf16_ulp_diff(y[:bs].cpu(), wy)
@@ -235,7 +236,7 @@ def _peer_worker(rank, world, port, q):
         dist.barrier()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
-            comm.allreduce_residual_rmsnorm(0, rows, n, rdev, w.to(dev), y, res, 1e-5, False)
+            comm.allreduce_residual_rmsnorm(0, rows, n, rdev, wd, y, res, 1e-5, False)
             comm.allreduce_residual_rmsnorm(1, rows, n, res, None, None, h, 0.0, True)
         for it in range(20):
             parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
@@ -257,12 +258,12 @@ def _peer_worker(rank, world, port, q):
         ro = torch.zeros_like(rs)
         lo, hi = rank * (rows // world), (rank + 1) * (rows // world)
         g2 = torch.cuda.CUDAGraph()
-        comm.allreduce_residual_rmsnorm(0, rows, n, rs, w.to(dev), yb, ro, 1e-5, True, sharded=True)     # warm-up
+        comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yb, ro, 1e-5, True, sharded=True)     # warm-up
         torch.cuda.synchronize()
         dist.barrier()
         with torch.cuda.graph(g2):
-            comm.allreduce_residual_rmsnorm(0, rows, n, rs, w.to(dev), yb, ro, 1e-5, True, sharded=True)
-            comm.allreduce_residual_rmsnorm(0, rows, n, ro, w.to(dev), yb, rs, 1e-5, False, sharded=True)
+            comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yb, ro, 1e-5, True, sharded=True)
+            comm.allreduce_residual_rmsnorm(0, rows, n, ro, wd, yb, rs, 1e-5, False, sharded=True)
         for it in range(10):
             parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
             r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
