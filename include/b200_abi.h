@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 7
+#define B200_ABI_VERSION 9
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -281,6 +281,10 @@ typedef struct b200_ar_args {
     int32_t timeout_ms;       /* flag wait bound; 0 = default 2000                 */
     int32_t mode;             /* 0 = one-shot, or B200_AR_MODE_ROW_SHARDED         */
     void*   y_peers[B200_AR_MAX_WORLD];  /* row-sharded: rank r's y buffer (entry `rank` == y) */
+    void*   xstage_peers[B200_AR_MAX_WORLD];  /* LL form: rank r's staging for pushed partial rows  */
+    void*   ystage_peers[B200_AR_MAX_WORLD];  /* LL form: rank r's staging for pushed normalised rows */
+    void*   trace;            /* optional uint64 [min(rows, MAX_CTAS)][4]: %globaltimer (ns) at kernel start, barrier
+                                 passed, rows reduced, end of every CTA (tools/bench_allreduce.py); NULL = off        */
 } b200_ar_args;
 
 /* Row-sharded ("two-shot") form for world > 1, rows <= B200_AR_MAX_CTAS: rank r OWNS rows
@@ -294,6 +298,16 @@ typedef struct b200_ar_args {
  * (total (B200_AR_MAX_WORLD + 1) * B200_AR_MAX_CTAS words); consecutive calls need NOT alternate
  * buffers (the done flag is the proof that the owner finished reading). */
 #define B200_AR_MODE_ROW_SHARDED 1
+
+/* LL push form (flag-in-data): row ownership and the row-sharded residual contract of ROW_SHARDED, but no
+ * remote loads, no flags, no fences.  Non-owners store their partial row into the owner's x staging as
+ * 16-byte packets {d0, epoch, d1, epoch}; the owner polls its own staging, reduces in rank order,
+ * normalises and stores y as packets into every rank's y staging; each rank unpacks its copy into the
+ * plain local `y`.  y / x need not alias peer-visible buffers except x_peers[rank] (the local partial sums).
+ * Staging (peer visible, zeroed once): x staging world * ceil(rows/world) * n * 4 bytes, y staging
+ * rows * n * 4 bytes.  epoch words [B200_AR_MAX_CTAS + 1] (call counter) and [+2] (arrival counter) are
+ * used: `epoch` must hold B200_AR_MAX_CTAS + 4 words. */
+#define B200_AR_MODE_LL 2
 
 int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
 

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 7
+ABI_VERSION = 9
 
 
 class DecodeArgs(C.Structure):
@@ -67,6 +67,7 @@ class PrefillArgs(C.Structure):
 
 AR_MAX_WORLD, AR_MAX_CTAS, IPC_HANDLE_BYTES = 8, 1024, 64
 AR_MODE_ROW_SHARDED = 1
+AR_MODE_LL = 2
 
 
 class ArArgs(C.Structure):
@@ -79,6 +80,7 @@ class ArArgs(C.Structure):
         ("eps", _f32), ("w_dtype", _i32), ("rank", _i32), ("world", _i32),
         ("ss_rounded", _i32), ("timeout_ms", _i32), ("mode", _i32),
         ("y_peers", _vp * AR_MAX_WORLD),
+        ("xstage_peers", _vp * AR_MAX_WORLD), ("ystage_peers", _vp * AR_MAX_WORLD), ("trace", _vp),
     ]
 
 

@@ -7,7 +7,8 @@ elementwise kernels that follow it at core/layer/model_graph.py:210-216 and :219
 One process per GPU.  Every rank cudaMalloc's ONE slab (IPC-exportable, outside torch's caching
 allocator), laid out as
 
-    [ flags u32[1024][8] + u32[1024] | epoch u32[1025] (local only) | pad | slot 0 | slot 1 | y ]
+    [ flags u32[1024][8] + u32[1024] | epoch u32[1028] (local only) | pad | slot 0 | slot 1 | y |
+      x staging (LL) | y staging (LL) ]
 
 exports it with cudaIpcGetMemHandle, exchanges the 64-byte handles through torch.distributed
 (plumbing only) and maps every peer's slab.  The two data slots are the GEMM output buffers the
@@ -27,7 +28,7 @@ from . import _lib
 from ._lib import ArArgs, check, lib
 
 _FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4        # ready flags [1024][8] + done flags [1024]
-_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 1) * 4 + 255) // 256 * 256
+_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 4) * 4 + 255) // 256 * 256     # per-CTA epochs, error word, LL call + arrival counters
 _HEADER = _FLAG_BYTES + _EPOCH_BYTES
 
 
@@ -97,7 +98,11 @@ class PeerComm:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.slot_bytes = (int(slot_bytes) + 255) // 256 * 256
         self.timeout_ms = int(timeout_ms)
-        total = _HEADER + 3 * self.slot_bytes
+        # LL staging: packets double the bytes; x staging holds world * ceil(rows / world) rows (<= rows + world)
+        self._xstage_off = _HEADER + 3 * self.slot_bytes
+        self._xstage_bytes = 2 * self.slot_bytes + self.world * 16384 * 4
+        self._ystage_off = self._xstage_off + self._xstage_bytes
+        total = self._ystage_off + 2 * self.slot_bytes
         with torch.cuda.device(self.device):
             p = C.c_void_p()
             check(lib.b200_comm_alloc(total, C.byref(p)), "b200_comm_alloc")
@@ -150,13 +155,13 @@ class PeerComm:
     def allreduce_residual_rmsnorm(self, slot_idx: int, rows: int, n: int, residual: Optional[torch.Tensor],
                                    weight: Optional[torch.Tensor], y: Optional[torch.Tensor],
                                    res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False,
-                                   sharded: bool = False):
+                                   sharded: bool = False, trace: Optional[torch.Tensor] = None, ll: bool = False):
         """res_out = bf16(bf16(sum over ranks of slot[slot_idx][:rows, :n]) + residual);
         y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable.
         ``sharded``: the row-sharded form (B200_AR_MODE_ROW_SHARDED) — ``y`` must be a prefix view of
         :meth:`ybuf`, rows <= 1024, and ``residual`` / ``res_out`` are only read / written for the rows
         this rank owns."""
-        if slot_idx == self._last_slot and not sharded:
+        if slot_idx == self._last_slot and not (sharded or ll):
             raise AssertionError("PeerComm: consecutive fused all-reduces must alternate slots 0 / 1")
         self._last_slot = slot_idx
         x = self.slot(slot_idx, rows, n)
@@ -176,6 +181,18 @@ class PeerComm:
             a.mode = _lib.AR_MODE_ROW_SHARDED
             for r in range(self.world):
                 a.y_peers[r] = self._peer_base[r] + yoff
+        if ll:
+            # LL push form: flag-in-data packets through the staging areas; y is any local tensor
+            assert not sharded and y is not None
+            R = -(-rows // self.world)
+            assert self.world * R * n * 4 <= self._xstage_bytes and rows * n * 4 <= 2 * self.slot_bytes
+            a.mode = _lib.AR_MODE_LL
+            for r in range(self.world):
+                a.xstage_peers[r] = self._peer_base[r] + self._xstage_off
+                a.ystage_peers[r] = self._peer_base[r] + self._ystage_off
+        if trace is not None:
+            assert trace.dtype == torch.int64 and trace.is_cuda and trace.numel() >= 4 * min(rows, _lib.AR_MAX_CTAS)
+            a.trace = trace.data_ptr()
         check(lib.b200_allreduce_residual_rmsnorm(C.byref(a), torch.cuda.current_stream().cuda_stream),
               "b200_allreduce_residual_rmsnorm")
         return y, res_out

@@ -95,6 +95,7 @@ class KVCacheManager:
             sl = torch.zeros(max_batch_size, dtype=torch.int32, pin_memory=self._on_gpu)
             self._stages.append({"bt": bt, "sl": sl, "bt_np": bt.numpy(), "sl_np": sl.numpy(), "event": None})
         self._stage_idx = 0
+        self.len_max_over_mean = 1.0
 
     # ------------------------------------------------------------------ allocator
     def alloc(self, seq_id: int, n_tokens: int) -> Tuple[bool, Optional[torch.Tensor]]:
@@ -192,6 +193,10 @@ class KVCacheManager:
                 if blocks:
                     bt[i, :len(blocks)] = blocks               # raises if a sequence outgrew max_tokens, like the reference
             stage["sl_np"][:B] = context_lens
+            # host-side hint for the decode runner: longest / mean context of this batch (ragged batches take
+            # the balanced attention schedule)
+            tot = float(sum(context_lens))
+            self.len_max_over_mean = (max(context_lens) * B / tot) if tot > 0 else 1.0
             self._block_table_buffer[:B].copy_(stage["bt"][:B], non_blocking=True)
             self._cache_seqlens_buffer[:B].copy_(stage["sl"][:B], non_blocking=True)
             if self._on_gpu:

@@ -77,6 +77,7 @@ class ModelGraphRunner:
         self.prepare_weights()
         self._alloc_bufs()
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
+        self._graphs_balanced: Dict[int, torch.cuda.CUDAGraph] = {}
         self._is_graph_ready = False
 
     # ------------------------------------------------------------------ init
@@ -127,17 +128,21 @@ class ModelGraphRunner:
         self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
         if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
             self._comm = None
-        # Row-sharded ("two-shot") reduction: each rank reduces + normalises only the rows it owns and pushes y to
-        # all ranks; the residual stream stays row-sharded, so it needs the final norm fused (ln_f is a kernel norm).
-        # B200_AR_SHARDED = 0 / 1 forces it; default: from 4 ranks up (at 2 ranks it moves the same bytes).
-        self._ar_sharded = False
+        # Reduction form (B200_AR_MODE = oneshot | sharded | ll; default ll from 4 ranks up when the final norm can be
+        # fused, else oneshot).  "ll" and "sharded" reduce + normalise each row on ONE owner rank and keep the residual
+        # stream row-sharded, so they need ln_f fused (a kernel norm); "ll" moves data as flag-in-data packets with
+        # remote stores only (no remote loads, no fences: ~2 one-way NVLink hops per call).
+        self._ar_mode = "oneshot"
         if self._comm is not None:
             self._attn_out = self._comm.slot(0, mb, self.hidden_dim)
             self._mlp_out = self._comm.slot(1, mb, self.hidden_dim)
-            want = os.environ.get("B200_AR_SHARDED", "auto")
-            fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False))
-            self._ar_sharded = fusable and mb <= 1024 and (want == "1" or (want == "auto" and self.world_size >= 4))
-            if self._ar_sharded:
+            want = os.environ.get("B200_AR_MODE", "auto")
+            fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
+            if want == "auto":
+                want = "ll" if self.world_size >= 4 else "oneshot"
+            if want in ("ll", "sharded") and fusable:
+                self._ar_mode = want
+            if self._ar_mode == "sharded":
                 self._normed = self._comm.ybuf(mb, self.hidden_dim)
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
 
@@ -150,7 +155,7 @@ class ModelGraphRunner:
             qkv.add_(block.attn._qkv_b)
         return qkv
 
-    def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache):
+    def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced=False):
         Hq, Hkv, D = self.num_heads, self.kv_num_heads, self.head_size
         q = qkv[:, : Hq * D].view(bs, Hq, D)
         k = qkv[:, Hq * D: (Hq + Hkv) * D].view(bs, Hkv, D)
@@ -163,7 +168,8 @@ class ModelGraphRunner:
         b200ops.paged_attn_decode(q, k_cache, v_cache, k, v,
                                   self.attention._cos_pool, self.attention._sin_pool,
                                   cache_lens, block_table, softmax_scale=self.attention.scale,
-                                  rotary_interleaved=False, out=attn, pdl=self.use_pdl)
+                                  rotary_interleaved=False, out=attn, pdl=0 if balanced else self.use_pdl,
+                                  balanced=balanced)
         out = self._attn_out[:bs]
         torch.matmul(self._attn[:bs], block.attn._o, out=out)
         return out
@@ -183,13 +189,14 @@ class ModelGraphRunner:
         if self._comm is not None:
             self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
                                                   y if norm is not None else None, res_out, eps, ss_rounded,
-                                                  sharded=self._ar_sharded)
+                                                  sharded=self._ar_mode == "sharded", ll=self._ar_mode == "ll")
         else:
             all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
             allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,
                                              ss_rounded)
 
-    def decode(self, input_ids, bs, cache_manager, use_graph_cache):
+    def decode(self, input_ids, bs, cache_manager, use_graph_cache, balanced=False):
+        """``balanced`` selects the persistent stream-K attention schedule (ragged batches)."""
         tr = self.model.transformer
         h = tr.wte(input_ids)
         normed, residual, h_buf = self._normed[:bs], self._residual[:bs], self._h[:bs]
@@ -199,7 +206,7 @@ class ModelGraphRunner:
         for layer_idx in range(self.num_layers):
             block = tr.h[layer_idx]
             qkv = self._qkv_proj(block, bs)
-            attn_out = self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache)
+            attn_out = self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced)
             # all_reduce + rmsnorm_residual_gemm (reference :210-216): sum of squares of the unrounded sum
             self._reduce_add_norm(0, attn_out, h, block.ln_2, normed, residual, ss_rounded=False)
             mlp_out = self._ffn(normed, block, bs)
@@ -210,28 +217,47 @@ class ModelGraphRunner:
             h = h_buf
         return self.model.lm_head(normed if fuse_ln_f else ln_f(h))
 
-    def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32]):
-        """3 eager warm-ups then ``torch.cuda.graph`` per batch size (reference :225-253)."""
+    # A batch whose longest sequence exceeds this multiple of the mean length is "ragged": the split-KV grid
+    # (one launch-constant split count for every row) leaves most SMs idle behind the long rows, the balanced
+    # persistent schedule does not (profiles/r01: 64 seqs log-uniform 128-32k, 413 us -> 147 us per layer call;
+    # on uniform batches the split grid stays ~20 % faster, so it remains the default).
+    RAGGED_RATIO = 1.5
+
+    def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32], ragged: bool = False):
+        """3 eager warm-ups then ``torch.cuda.graph`` per batch size (reference :225-253).  ``ragged`` also
+        captures, for every batch size > 1, a second graph whose attention uses the balanced schedule;
+        ``forward`` replays it when the cache manager reports a ragged batch."""
         if self._is_graph_ready:
             return
         for bs in batch_sizes:
-            dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
-            with torch.no_grad():
-                for _ in range(3):
-                    self.decode(dummy, bs, cache_manager, use_graph_cache=False)
-            torch.cuda.synchronize()
-            g = torch.cuda.CUDAGraph()
-            with torch.no_grad(), torch.cuda.graph(g):
-                self._logits[:bs] = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True)
-            self._graphs[bs] = g
-            logger.info("captured decode graph for batch size %d", bs)
+            for balanced in ((False, True) if ragged and bs > 1 and bs <= 512 else (False,)):
+                dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
+                with torch.no_grad():
+                    for _ in range(3):
+                        self.decode(dummy, bs, cache_manager, use_graph_cache=False, balanced=balanced)
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.no_grad(), torch.cuda.graph(g):
+                    self._logits[:bs] = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True,
+                                                    balanced=balanced)
+                if balanced:
+                    self._graphs_balanced[bs] = g
+                else:
+                    self._graphs[bs] = g
+                logger.info("captured decode graph for batch size %d%s", bs, " (balanced)" if balanced else "")
         self._is_graph_ready = True
+
+    def _is_ragged(self, cache_manager, batch_size: int) -> bool:
+        ratio = getattr(cache_manager, "len_max_over_mean", None)     # set by KVCacheManager.cache_batch_data
+        return batch_size > 1 and ratio is not None and ratio >= self.RAGGED_RATIO
 
     def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
         self._input_ids[:batch_size] = input_ids
-        g = self._graphs.get(batch_size)
+        ragged = self._is_ragged(cache_manager, batch_size)
+        g = (self._graphs_balanced.get(batch_size) if ragged else None) or self._graphs.get(batch_size)
         if g is None:
             with torch.no_grad():
-                return self.decode(input_ids, batch_size, cache_manager, use_graph_cache=True)
+                return self.decode(input_ids, batch_size, cache_manager, use_graph_cache=True,
+                                   balanced=ragged and batch_size <= 512)
         g.replay()
         return self._logits[:batch_size]

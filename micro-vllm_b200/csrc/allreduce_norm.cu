@@ -34,14 +34,33 @@ struct ArParams {
     long long timeout_cycles;
     __nv_bfloat16* yp[B200_AR_MAX_WORLD];   // row-sharded form: every rank's y buffer (entry `rank` is local)
     int rows_per_rank;                      // row-sharded form: rank r owns rows [r * rows_per_rank, ...)
+    uint8_t* xstage[B200_AR_MAX_WORLD];     // LL form: every rank's staging area for pushed partial rows
+    uint8_t* ystage[B200_AR_MAX_WORLD];     // LL form: every rank's staging area for pushed normalised rows
+    unsigned long long* trace;              // optional [grid][4] %globaltimer stamps: start, barrier passed, row reduced, end
 };
+
+__device__ __forceinline__ void stamp(const ArParams& p, int slot) {
+    if (p.trace != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(size_t)blockIdx.x * 4 + slot] = t;
+    }
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+// Flags that announce data written by an EARLIER kernel of the sender's stream need no fence: a kernel boundary
+// already made those writes visible in the sender's L2, which is where peers read them.  System-scope
+// release / acquire on every flag costs 3-6 us when 64 CTAs fence at once (profiles/r01/allreduce_tp2.json),
+// so those flags are relaxed system-scope (volatile) stores and polls; only flags that publish data written
+// by THIS kernel (the row-sharded form's "done" flag) are release stores.
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 // peer data: never served from a stale L1 line (the same addresses carry new data every step)
@@ -72,7 +91,7 @@ template <> struct ArW<float> {
 // bounded wait for flag >= e (signed distance: the epoch may wrap)
 __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t e, const ArParams& p) {
     const long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(flag) - e) < 0) {
+    while ((int32_t)(ld_relaxed_sys(flag) - e) < 0) {
         if (clock64() - t0 > p.timeout_cycles) {              // a peer never arrived: flag it, do not hang the GPU
             atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u);
             break;
@@ -92,6 +111,7 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
     const int bid = blockIdx.x;
     const int T = blockDim.x;
     const int nvec = (int)(p.n >> 3);
+    stamp(p, 0);
 
     if (TS) {
         const uint32_t e = p.epoch[bid] + 1u;
@@ -99,9 +119,10 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
         uint32_t* ready = p.flags[owner] + bid * B200_AR_MAX_WORLD;                       // on the owner: [row][src rank]
         if (owner != p.rank) {
             if (threadIdx.x != 0) return;
-            st_release_sys(ready + p.rank, e);                                            // my partial sums of this row are written
+            st_relaxed_sys(ready + p.rank, e);                                            // my partial sums of this row are written (previous kernel)
             wait_flag(p.flags[p.rank] + B200_AR_MAX_CTAS * B200_AR_MAX_WORLD + bid, e, p); // owner pushed y (and is done with my x)
             p.epoch[bid] = e;
+            stamp(p, 3);
             return;
         }
         if (threadIdx.x < WS && threadIdx.x != p.rank) wait_flag(ready + threadIdx.x, e, p);
@@ -111,15 +132,16 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
         const uint32_t e = p.epoch[bid] + 1u;
         if (threadIdx.x < WS) {
             const int peer = threadIdx.x;
-            // everything this rank's stream wrote before this kernel (the GEMM that produced x) is ordered
-            // before the flag by the release; the peer's acquire + its CTA barrier orders its loads after it
-            st_release_sys(p.flags[peer] + bid * B200_AR_MAX_WORLD + p.rank, e);
+            // x was written by the GEMM kernel that precedes this one in the stream (see st_relaxed_sys); the
+            // peer's volatile data loads follow its poll in program order behind the CTA barrier
+            st_relaxed_sys(p.flags[peer] + bid * B200_AR_MAX_WORLD + p.rank, e);
             wait_flag(p.flags[p.rank] + bid * B200_AR_MAX_WORLD + peer, e, p);
         }
         __syncthreads();
         if (threadIdx.x == 0) p.epoch[bid] = e;
     }
 
+    stamp(p, 1);
     const bool has_r = p.r != nullptr;
     const bool norm = p.w != nullptr;
     for (int64_t row = bid; row < p.rows; row += gridDim.x) {
@@ -202,11 +224,216 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
             }
         }
     }
+    stamp(p, 2);
     if (TS) {
         __syncthreads();                                     // every thread's pushes are ordered before the release below
         if (threadIdx.x < WS && threadIdx.x != p.rank)
             st_release_sys(p.flags[threadIdx.x] + B200_AR_MAX_CTAS * B200_AR_MAX_WORLD + bid, p.epoch[bid]);
     }
+    stamp(p, 3);
+}
+
+// ------------------------------------------------------------------ LL push form (flag-in-data, no fences)
+// Measured on 2 x B200 (profiles/r01/allreduce_tp2.json): a system-scope release/acquire flag hop costs
+// 3-6 us when 64 CTAs fence at once and a remote LOAD round trip over NVLink ~3.4 us, so the pull forms
+// above spend ~9 us per call before moving a byte.  This form never loads remote memory and never
+// fences: data travels as 16-byte packets {d0, epoch, d1, epoch} written with remote STORES (8-byte
+// halves are single-copy atomic: a packet whose two flags equal the call's epoch carries valid data —
+// NCCL's LL protocol), and receivers poll packets in their OWN memory.
+//   CTA of row i on a rank that does not own row i:  pushes its partial row to the owner's staging area,
+//       then polls its own y staging for the owner's normalised row and writes it out as plain bf16.
+//   CTA of row i on the owner: polls the world-1 staged rows, sums in rank order with its own row, adds its
+//       residual row, normalises, writes res_out / y locally and pushes y as packets to every rank.
+// Two one-way hops per call, (world-1)/world of an activation (x 2 for the flags) per direction per rank.
+// The epoch is ONE counter per rank, advanced by the last CTA of every call, so stale packets (older calls,
+// other row partitions) can never match.  The residual stream stays row-sharded as in the sharded form.
+__device__ __forceinline__ void st_ll(void* p, uint32_t d0, uint32_t d1, uint32_t e) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(d0), "r"(e), "r"(d1), "r"(e) : "memory");
+}
+__device__ __forceinline__ bool ll_ready(const uint4& v, uint32_t e) { return v.y == e && v.w == e; }
+
+// One 16-byte vector (8 bf16) from each of N sources in order; source `self` (if 0 <= self < N) is a plain local
+// row, the others are LL-staged rows (2 packets).  Every load is issued first, late packets are re-polled.
+template <int N>
+__device__ __forceinline__ void ll_gather(const uint8_t* (&src)[N], int self, uint32_t e, const ArParams& p, uint4 (&out)[N]) {
+    uint4 pk[N][2];
+#pragma unroll
+    for (int s = 0; s < N; ++s) {
+        if (s == self) { pk[s][0] = ld_v4(src[s]); pk[s][1] = pk[s][0]; }
+        else           { pk[s][0] = ld_peer_v4(src[s]); pk[s][1] = ld_peer_v4(src[s] + 16); }
+    }
+#pragma unroll
+    for (int s = 0; s < N; ++s) {
+        if (s == self) { out[s] = pk[s][0]; continue; }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (!ll_ready(pk[s][h], e)) {
+                const long long t0 = clock64();
+                do {
+                    pk[s][h] = ld_peer_v4(src[s] + 16 * h);
+                    if (clock64() - t0 > p.timeout_cycles) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+                } while (!ll_ready(pk[s][h], e));
+            }
+        }
+        out[s] = make_uint4(pk[s][0].x, pk[s][0].z, pk[s][1].x, pk[s][1].z);
+    }
+}
+
+template <int WS, int VPT, typename WT>
+__global__ void __launch_bounds__(512)
+allreduce_ll_kernel(const __grid_constant__ ArParams p) {
+    __shared__ float red[32];
+    const int row = blockIdx.x;                              // grid = rows
+    const int T = blockDim.x;
+    const int nvec = (int)(p.n >> 3);
+    stamp(p, 0);
+    const uint32_t e = p.epoch[B200_AR_MAX_CTAS + 1] + 1u;   // one epoch per call, the same on every rank
+    const int R = p.rows_per_rank;
+    const int owner = row / R, j = row - owner * R;
+    const size_t row_stage = (size_t)nvec * 32;              // bytes of one staged row (2 packets per 16-byte vector)
+
+    if (owner != p.rank) {
+        // ---- push my partial row to the owner, then receive the normalised row
+        uint8_t* dst = p.xstage[owner] + ((size_t)p.rank * R + j) * row_stage;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                const uint4 x = ld_v4(p.x[p.rank] + (int64_t)row * p.sx + (int64_t)v * 8);
+                st_ll(dst + (size_t)v * 32, x.x, x.y, e);
+                st_ll(dst + (size_t)v * 32 + 16, x.z, x.w, e);
+            }
+        }
+        stamp(p, 1);
+        const uint8_t* ysrc = p.ystage[p.rank] + (size_t)row * row_stage;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                const uint8_t* srcs[1] = {ysrc + (size_t)v * 32};
+                uint4 o[1];
+                ll_gather<1>(srcs, -1, e, p, o);
+                st_na_v4(p.y + (int64_t)row * p.sy + (int64_t)v * 8, o[0]);
+            }
+        }
+        stamp(p, 2);
+    } else {
+        // ---- owner: gather the staged partial rows (local memory), reduce in rank order, normalise, push y
+        const bool has_r = p.r != nullptr;
+        float ss = 0.0f;
+        float f[VPT][8];
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                const uint8_t* srcs[WS];
+#pragma unroll
+                for (int s = 0; s < WS; ++s)
+                    srcs[s] = (s == p.rank)
+                        ? reinterpret_cast<const uint8_t*>(p.x[p.rank] + (int64_t)row * p.sx + (int64_t)v * 8)
+                        : p.xstage[p.rank] + ((size_t)s * R + j) * row_stage + (size_t)v * 32;
+                uint4 rv = make_uint4(0u, 0u, 0u, 0u);
+                if (has_r) rv = ld_v4(p.r + (int64_t)row * p.sr + (int64_t)v * 8);
+                uint4 got[WS];
+                ll_gather<WS>(srcs, p.rank, e, p, got);
+                uint4 ro;
+                uint32_t* pro = &ro.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float a = bf16lo((&got[0].x)[k]), b = bf16hi((&got[0].x)[k]);
+#pragma unroll
+                    for (int q = 1; q < WS; ++q) {           // fixed rank order 0 .. world-1 (the one-shot form's order)
+                        a += bf16lo((&got[q].x)[k]);
+                        b += bf16hi((&got[q].x)[k]);
+                    }
+                    const uint32_t s2 = pack_bf16(a, b);     // what all_reduce hands back is a bf16 tensor
+                    a = bf16lo(s2); b = bf16hi(s2);
+                    if (has_r) { a += bf16lo((&rv.x)[k]); b += bf16hi((&rv.x)[k]); }
+                    const uint32_t pk = pack_bf16(a, b);
+                    pro[k] = pk;
+                    const float ar = bf16lo(pk), br = bf16hi(pk);
+                    if (p.ss_rounded) { ss += ar * ar; ss += br * br; }
+                    else              { ss += a * a;   ss += b * b; }
+                    f[i][2 * k] = ar; f[i][2 * k + 1] = br;
+                }
+                st_na_v4(p.res_out + (int64_t)row * p.sres + (int64_t)v * 8, ro);
+            }
+        }
+        stamp(p, 1);
+        {
+            const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+            const int nw = (T + 31) >> 5;
+            ss = warp_sum(ss);
+            if (nw > 1) {
+                if (lane == 0) red[wid] = ss;
+                __syncthreads();
+                float t = (lane < nw) ? red[lane] : 0.0f;
+                ss = warp_sum(t);
+            }
+        }
+        const float rrms = rsqrtf(ss / (float)p.n + p.eps);
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                float wf[8];
+                ArW<WT>::load8(p.w, (int64_t)v * 8, wf);
+                uint4 o;
+                uint32_t* po = &o.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
+#pragma unroll
+                for (int k = 0; k < WS; ++k) {
+                    if (k == p.rank) continue;
+                    uint8_t* dst = p.ystage[k] + (size_t)row * row_stage + (size_t)v * 32;
+                    st_ll(dst, o.x, o.y, e);
+                    st_ll(dst + 16, o.z, o.w, e);
+                }
+                st_na_v4(p.y + (int64_t)row * p.sy + (int64_t)v * 8, o);
+            }
+        }
+        stamp(p, 2);
+    }
+    // the last CTA of the call advances the epoch (every CTA has read it before it can arrive here)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned done = atomicAdd(p.epoch + B200_AR_MAX_CTAS + 2, 1u);
+        if (done == gridDim.x - 1) {
+            p.epoch[B200_AR_MAX_CTAS + 2] = 0u;
+            __threadfence();
+            p.epoch[B200_AR_MAX_CTAS + 1] = e;
+        }
+    }
+    stamp(p, 3);
+}
+
+template <int WS, typename WT>
+static int launch_ll(const ArParams& p, cudaStream_t st) {
+    const int64_t nvec = p.n / 8;
+    const unsigned grid = (unsigned)p.rows;
+    if (nvec <= 512) {
+        const int threads = (int)((nvec + 31) & ~31LL);
+        allreduce_ll_kernel<WS, 1, WT><<<grid, threads, 0, st>>>(p);
+    } else if (nvec <= 1024) {
+        const int threads = (int)(((nvec + 1) / 2 + 31) & ~31LL);
+        allreduce_ll_kernel<WS, 2, WT><<<grid, threads, 0, st>>>(p);
+    } else {
+        const int threads = (int)(((nvec + 3) / 4 + 31) & ~31LL);
+        allreduce_ll_kernel<WS, 4, WT><<<grid, threads, 0, st>>>(p);
+    }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename WT>
+static int dispatch_ll(int world, const ArParams& p, cudaStream_t st) {
+    switch (world) {
+        case 2: return launch_ll<2, WT>(p, st);
+        case 4: return launch_ll<4, WT>(p, st);
+        case 8: return launch_ll<8, WT>(p, st);
+    }
+    B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: LL form needs world 2, 4 or 8 (got %d)", world);
 }
 
 template <int WS, typename WT, bool TS>
@@ -292,6 +519,21 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
         if (p.rows_per_rank < 1) p.rows_per_rank = 1;
     }
+    const bool ll = (a->mode & B200_AR_MODE_LL) != 0;
+    if (ll) {
+        if (sharded) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: choose one of ROW_SHARDED / LL");
+        if (a->world < 2) B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: LL form needs world > 1");
+        if (a->rows > 65535) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: LL form handles at most 65535 rows");
+        if (!a->weight) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: LL form needs the norm (weight, y)");
+        for (int r = 0; r < a->world; ++r) {
+            if (!a->xstage_peers[r] || !a->ystage_peers[r] || !aligned16(a->xstage_peers[r]) || !aligned16(a->ystage_peers[r]))
+                B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: staging pointers of rank %d missing or unaligned", r);
+            p.xstage[r] = (uint8_t*)a->xstage_peers[r];
+            p.ystage[r] = (uint8_t*)a->ystage_peers[r];
+        }
+        p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
+        if (p.rows_per_rank < 1) p.rows_per_rank = 1;
+    }
     if (a->rows == 0) return 0;
     p.epoch = (uint32_t*)a->epoch;
     p.r = (const __nv_bfloat16*)a->residual;
@@ -303,7 +545,13 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
     p.eps = a->eps; p.rank = a->rank; p.ss_rounded = a->ss_rounded ? 1 : 0;
     const int ms = a->timeout_ms > 0 ? a->timeout_ms : 2000;
     p.timeout_cycles = (long long)ms * 2000000LL;          // ~2 GHz SM clock upper bound
+    p.trace = (unsigned long long*)a->trace;
     cudaStream_t st = (cudaStream_t)stream;
+    if (ll) {
+        if (a->w_dtype == B200_DT_F32) return dispatch_ll<float>(a->world, p, st);
+        if (a->w_dtype == B200_DT_BF16) return dispatch_ll<__nv_bfloat16>(a->world, p, st);
+        B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
+    }
     if (a->weight && a->w_dtype == B200_DT_F32) return dispatch_ws<float>(a->world, sharded, p, st);
     if (!a->weight || a->w_dtype == B200_DT_BF16) return dispatch_ws<__nv_bfloat16>(a->world, sharded, p, st);
     B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);

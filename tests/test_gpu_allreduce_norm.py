@@ -162,6 +162,66 @@ def test_row_sharded_emulated_single_gpu(world, rows, n):
     assert all(torch.equal(ys[0], y) for y in ys[1:])
 
 
+def _ll_encode(rows_bf16, e):
+    """[r, n] bf16 -> LL staging rows int32 [r, n]: data words interleaved with the epoch ({d0, e, d1, e} packets)."""
+    d = rows_bf16.contiguous().view(torch.int32)
+    out = torch.empty(d.shape[0], d.shape[1] * 2, dtype=torch.int32)
+    out[:, 0::2] = d
+    out[:, 1::2] = e
+    return out
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("rows,n", [(64, 8192), (5, 3584), (1, 896), (3, 16384), (100, 512)])
+def test_ll_push_emulated_single_gpu(world, rows, n):
+    """LL push form, one 'rank' per launch: what the peers would have pushed (their partial rows into this
+    rank's x staging, the other owners' normalised rows into its y staging) is encoded on the host; the
+    launch must produce the full plain y, res_out for its own rows, and push the right packets to the others."""
+    from b200ops import _lib
+    parts, r, w = _inputs(rows, n, world, world * 131 + rows + n)
+    wy, wres = allreduce_residual_rmsnorm_oracle(parts, r, w, 1e-5, True)
+    R = -(-rows // world)
+    e = 1
+    for rank in range(world):
+        lo, hi = min(rows, rank * R), min(rows, (rank + 1) * R)
+        xst = [torch.zeros(world * R, n, dtype=torch.int32, device="cuda") for _ in range(world)]
+        yst = [torch.zeros(rows, n, dtype=torch.int32, device="cuda") for _ in range(world)]
+        for src in range(world):                            # peers' pushes into THIS rank's x staging
+            if src != rank and hi > lo:
+                xst[rank][src * R: src * R + (hi - lo)] = _ll_encode(parts[src][lo:hi], e).cuda()
+        mask = torch.ones(rows, dtype=torch.bool)
+        mask[lo:hi] = False
+        yst[rank][mask] = _ll_encode(wy[mask], e).cuda()    # the other owners' rows arrive in this rank's y staging
+        epoch = torch.zeros(_lib.AR_MAX_CTAS + 4, dtype=torch.int32, device="cuda")
+        y = torch.full((rows, n), 7.0, dtype=torch.bfloat16, device="cuda")
+        res = torch.full((rows, n), 5.0, dtype=torch.bfloat16, device="cuda")
+        xloc, rd, wd = parts[rank].cuda(), r.cuda(), w.cuda()
+        a = _lib.ArArgs()
+        for k in range(world):
+            a.x_peers[k] = xloc.data_ptr()                  # only entry `rank` is read in this form
+            a.flag_peers[k] = epoch.data_ptr()              # unused
+            a.xstage_peers[k], a.ystage_peers[k] = xst[k].data_ptr(), yst[k].data_ptr()
+        a.epoch = epoch.data_ptr()
+        a.residual, a.weight, a.y, a.res_out = rd.data_ptr(), wd.data_ptr(), y.data_ptr(), res.data_ptr()
+        a.rows, a.n = rows, n
+        a.stride_x = a.stride_r = a.stride_y = a.stride_res = n
+        a.eps, a.w_dtype, a.rank, a.world, a.ss_rounded, a.mode = 1e-5, _lib.DT_BF16, rank, world, 1, _lib.AR_MODE_LL
+        _lib.check(_lib.lib.b200_allreduce_residual_rmsnorm(C.byref(a), torch.cuda.current_stream().cuda_stream), "ar ll")
+        torch.cuda.synchronize()
+        assert int(epoch[_lib.AR_MAX_CTAS]) == 0 and int(epoch[_lib.AR_MAX_CTAS + 1]) == 1 and int(epoch[_lib.AR_MAX_CTAS + 2]) == 0
+        _ulp_ok(y, wy)                                       # full plain y: own rows computed, the rest unpacked
+        assert torch.equal(y[mask.cuda()].cpu(), wy[mask])
+        assert torch.equal(res[lo:hi].cpu(), wres[lo:hi]) and res[:lo].eq(5.0).all() and res[hi:].eq(5.0).all()
+        for k in range(world):
+            if k == rank:
+                continue
+            klo, khi = min(rows, k * R), min(rows, (k + 1) * R)
+            if khi > klo:                                    # my partial rows of k's block sit in k's x staging, slot `rank`
+                assert torch.equal(xst[k][rank * R: rank * R + (khi - klo)].cpu(), _ll_encode(parts[rank][klo:khi], e))
+            if hi > lo:                                      # my normalised rows were pushed into k's y staging
+                assert torch.equal(yst[k][lo:hi].cpu(), _ll_encode(y[lo:hi].cpu(), e))
+
+
 def test_flag_wait_is_bounded():
     """No peer ever signals: the kernel must come back (error word set), not hang the GPU."""
     from b200ops import _lib
@@ -279,6 +339,31 @@ def _peer_worker(rank, world, port, q):
             assert torch.equal(ro[lo:hi].cpu(), wres1[lo:hi]) and torch.equal(rs[lo:hi].cpu(), wres2[lo:hi]), f"sharded replay {it}"
             assert int(bf16_ulp_diff(yb.cpu(), wy2).max()) <= 1
         del g2
+        # LL push form: same contract as the sharded form, y is a plain local tensor; stale packets never match
+        yl = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
+        g3 = torch.cuda.CUDAGraph()
+        for bs in (rows, 7, rows):                            # row partitions change between calls
+            comm.allreduce_residual_rmsnorm(0, bs, n, rs[:bs], wd, yl[:bs], ro[:bs], 1e-5, True, ll=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        with torch.cuda.graph(g3):
+            comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yl, ro, 1e-5, True, ll=True)
+            comm.allreduce_residual_rmsnorm(0, rows, n, ro, wd, yl, rs, 1e-5, False, ll=True)
+        for it in range(10):
+            parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
+            r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
+            xs[0].copy_(parts0[rank].to(dev))
+            rs.copy_(r.to(dev))
+            torch.cuda.synchronize()
+            dist.barrier()
+            g3.replay()
+            torch.cuda.synchronize()
+            dist.barrier()
+            wy1, wres1 = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, True)
+            wy2, wres2 = allreduce_residual_rmsnorm_oracle(parts0, wres1, w, 1e-5, False)
+            assert torch.equal(ro[lo:hi].cpu(), wres1[lo:hi]) and torch.equal(rs[lo:hi].cpu(), wres2[lo:hi]), f"ll replay {it}"
+            assert int(bf16_ulp_diff(yl.cpu(), wy2).max()) <= 1
+        del g3
         assert comm.error_flag() == 0
         with pytest.raises(AssertionError):                          # same slot twice in a row is refused on the host
             comm._last_slot = 1

@@ -159,3 +159,45 @@ def test_graph_capture_batch_sizes_llama_shape(bs):
                                               feed=toks_g)
     spread = ref_logits.std().item()
     assert (logits_g - ref_logits).abs().max().item() < 0.05 * spread
+
+
+def test_ragged_batch_replays_balanced_graph():
+    """Continuous-batching style decode: sequences of very different lengths in one batch.  With
+    ``capture(ragged=True)`` the runner holds a second graph per batch size whose attention uses the
+    balanced persistent schedule and replays it when ``cache_batch_data`` reports max/mean >= 1.5;
+    logits must agree with the split-grid graph (same inputs) and with the reference path."""
+    shape = SHAPES["llama3-8b"]
+    lens = [40, 900, 90, 300]
+    B = len(lens)
+    out = {}
+    for ragged in (True, False):
+        model, dec, pre, mgr = make_runners(shape, 2, max_bs=B, vocab=2048, seed=3, n_blocks=80)
+        mgr.reset()
+        dec.capture(mgr, batch_sizes=[B], ragged=ragged)
+        assert (B in dec._graphs_balanced) == ragged and B in dec._graphs
+        g = torch.Generator().manual_seed(5)
+        prompts = [torch.randint(0, 2048, (1, P), generator=g) for P in lens]
+        first = []
+        for s, P in enumerate(lens):                       # per-sequence prefill (row 0 of the static tables each time)
+            ok, _ = mgr.alloc(s, P)
+            assert ok
+            mgr.cache_batch_data([s], [P])
+            with torch.no_grad():
+                lg = pre.forward(prompts[s].cuda(), mgr, 1)
+            first.append(lg[0, -1].float().argmax(-1))
+        tok = torch.stack(first)
+        ids = list(range(B))
+        steps = []
+        for i in range(4):
+            for s in ids:
+                mgr.append(s)
+            mgr.cache_batch_data(ids, [P + 1 + i for P in lens])
+            assert mgr.len_max_over_mean > 1.5
+            assert dec._is_ragged(mgr, B)
+            lg = dec.forward(tok, mgr, B).float().clone()
+            steps.append(lg.cpu())
+            tok = lg.argmax(-1)
+        out[ragged] = torch.stack(steps)
+    spread = out[False].std().item()
+    assert (out[True][0] - out[False][0]).abs().max().item() < 0.05 * spread      # step 0: identical inputs
+    assert torch.equal(out[True][0].argmax(-1), out[False][0].argmax(-1))

@@ -1,0 +1,118 @@
+"""Latency of the decode-path reduction alone on WORLD_SIZE GPUs (no GEMMs, no skew source):
+[rows, n] bf16 partial sums -> all-reduce + residual + RMSNorm, back to back in a CUDA graph.
+
+  one-shot : b200_allreduce_residual_rmsnorm (every rank loads all ranks' slots)
+  sharded  : row-sharded form (owner reduces its rows, pushes y to all ranks)
+  ll       : LL push form (flag-in-data packets, remote stores only)
+  nccl     : dist.all_reduce + the local fused residual+norm kernel (B200_FUSED_ALLREDUCE=0 path)
+
+Also prints the in-kernel %globaltimer phases of the fused forms (mean over CTAs of rank 0, last
+call): start -> barrier passed -> rows reduced -> end.  Time = CUDA events around graph replays,
+max over ranks.
+
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29571 tools/bench_allreduce.py
+"""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "micro-vllm_b200"), ROOT]
+import torch  # noqa: E402
+
+
+def main():
+    import torch.distributed as dist
+    from b200ops.comm import allreduce_residual_rmsnorm_local
+    from core import parallel_config as pc
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    pc.setup()
+    n = 8192
+    max_rows = 64
+    comm = pc.peer_comm(max_rows * n * 2)
+    calls = 40                                              # per graph (even: slots alternate 0, 1, 0, 1 ...)
+    out = []
+    w = torch.ones(n, dtype=torch.bfloat16, device=dev)
+    for rows in (64, 32, 8, 1):
+        res_a = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
+        res_b = torch.zeros_like(res_a)
+        y_loc = torch.empty_like(res_a)
+        yb = comm.ybuf(max_rows, n)[:rows]
+        trace = torch.zeros(4 * rows, dtype=torch.int64, device=dev)
+        for s in (0, 1):
+            comm.slot(s, max_rows, n)[:rows].normal_()
+        xs = [comm.slot(0, max_rows, n)[:rows], comm.slot(1, max_rows, n)[:rows]]
+        nccl_x = [torch.randn(rows, n, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+
+        def fused(mode, tr=None):
+            for c in range(calls):
+                comm.allreduce_residual_rmsnorm(c & 1, rows, n, res_a if c & 1 == 0 else res_b, w,
+                                                yb if mode == "sharded" else y_loc, res_b if c & 1 == 0 else res_a, 1e-5,
+                                                bool(c & 1), sharded=mode == "sharded", ll=mode == "ll",
+                                                trace=tr if c == calls - 1 else None)
+
+        def nccl():
+            for c in range(calls):
+                x = nccl_x[c & 1]
+                dist.all_reduce(x)
+                allreduce_residual_rmsnorm_local(x, res_a if c & 1 == 0 else res_b, w, y_loc,
+                                                 res_b if c & 1 == 0 else res_a, 1e-5, bool(c & 1))
+
+        def time_graph(fn, reps=10):
+            fn()
+            torch.cuda.synchronize()
+            dist.barrier()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            g.replay()
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) * 1e3 / (reps * calls)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.barrier()
+            del g
+            return float(t.item())
+
+        row = {"world": world, "rows": rows, "n": n, "bytes_per_rank": rows * n * 2}
+        for name in ("oneshot", "sharded", "ll"):
+            row[name + "_us"] = round(time_graph(lambda: fused(name)), 2)
+            trace.zero_()
+            fused(name, trace)
+            torch.cuda.synchronize()
+            dist.barrier()
+            t = trace.view(rows, 4).double()
+            own = t[:, 2] > 0                                # CTAs that stamped the "reduced" phase
+            if own.any():
+                tt = t[own]
+                row[name + "_phases_us"] = {"barrier": round(float((tt[:, 1] - tt[:, 0]).mean()) / 1e3, 2),
+                                            "reduce": round(float((tt[:, 2] - tt[:, 1]).mean()) / 1e3, 2),
+                                            "tail": round(float((tt[:, 3] - tt[:, 2]).mean()) / 1e3, 2),
+                                            "kernel_span": round(float(t[:, 3].max() - t[:, 0].min()) / 1e3, 2)}
+        row["nccl_us"] = round(time_graph(nccl), 2)
+        out.append(row)
+        if rank == 0:
+            print(json.dumps(row), flush=True)
+    assert comm.error_flag() == 0
+    if rank == 0:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"allreduce_tp{world}.json"), "w") as f:
+            json.dump(out, f, indent=1)
+    torch.cuda.synchronize()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

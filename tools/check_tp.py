@@ -83,7 +83,7 @@ def main():
     os.environ["B200_FUSED_ALLREDUCE"] = "1"
     comm = pc.peer_comm(1)
     err = comm.error_flag() if comm is not None else -1
-    res = {"world": world, "ranks_bit_identical": bool(same), "rel_rms_fused_vs_nccl_step0": round(rel0, 5),
+    res = {"world": world, "ar_mode": os.environ.get("B200_AR_MODE", "auto"), "ranks_bit_identical": bool(same), "rel_rms_fused_vs_nccl_step0": round(rel0, 5),
            "timeout_flag": err}
     if rank == 0:
         print(json.dumps(res), flush=True)

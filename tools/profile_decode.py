@@ -13,6 +13,7 @@ B, Hq, Hkv, D, ctx, page = 32, 32, 8, 128, 4096, 256
 n_launch = int(sys.argv[1]) if len(sys.argv) > 1 else 6
 variant = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 splits = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+balanced = bool(int(sys.argv[4])) if len(sys.argv) > 4 else False
 dev = torch.device("cuda")
 per_seq = ctx // page
 n_blocks = B * per_seq + 4
@@ -29,6 +30,7 @@ cos, sin = cos[:, : D // 2].contiguous().to(dev), sin[:, : D // 2].contiguous().
 out = torch.empty(B, Hq, D, device=dev, dtype=torch.bfloat16)
 for i in range(n_launch):
     kc, vc = caches[i % 3]
-    b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, out=out, variant=variant, num_splits=splits)
+    b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, out=out, variant=variant, num_splits=splits,
+                              balanced=balanced)
 torch.cuda.synchronize()
 print("done", n_launch, float(out.float().abs().mean()))
