@@ -37,7 +37,7 @@ def main():
     calls = 40                                              # per graph (even: slots alternate 0, 1, 0, 1 ...)
     out = []
     w = torch.ones(n, dtype=torch.bfloat16, device=dev)
-    for rows in (64, 32, 8, 1):
+    for rows in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else '64,32,8,1').split(',')]:
         res_a = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
         res_b = torch.zeros_like(res_a)
         y_loc = torch.empty_like(res_a)
