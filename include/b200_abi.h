@@ -230,6 +230,11 @@ int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D
 
 int b200_paged_attn_prefill(const b200_prefill_args* args, void* stream);
 
+/* Debug / profiling hook, not part of the operator surface: while `dev_buf` (device memory,
+ * 16 * 64 int64) is non-NULL every prefill launch records clock64 stamps of the pipeline
+ * hand-offs of CTA (0,0,0) into it (tools/trace_prefill.py); NULL switches it off. */
+void b200_debug_prefill_trace(void* dev_buf);
+
 /* ------------------------------------------------------------------------ *
  * Peer-memory all-reduce fused with the residual add and the RMSNorm that
  * follow it — replaces, in ONE launch per call site,

@@ -101,6 +101,7 @@ SIGNATURES = {
     "b200_lse_combine": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp]),
     "b200_prefill_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200_paged_attn_prefill": (C.c_int, [C.POINTER(PrefillArgs), _vp]),
+    "b200_debug_prefill_trace": (None, [_vp]),
     "b200_allreduce_residual_rmsnorm": (C.c_int, [C.POINTER(ArArgs), _vp]),
     "b200_comm_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
     "b200_comm_free": (C.c_int, [_vp]),

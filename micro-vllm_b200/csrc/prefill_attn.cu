@@ -20,6 +20,10 @@
 #include <cuda.h>
 #include <math_constants.h>
 
+#ifndef B200_PREFILL_DEFAULT_SM
+#define B200_PREFILL_DEFAULT_SM 2   // softmax arithmetic of variant 0: packed fp32x2 + 25 % polynomial exp2 (fastest, profiles/r01/prefill_bench.json)
+#endif
+
 namespace b200 {
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -55,6 +59,15 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" :: "l"(map) : "memory");
+}
+// One lane of a converged warp (warp-uniform control flow around it keeps the UMMA / TMA operands in
+// uniform registers; a divergent `if (lane == 0)` region makes the compiler wrap EVERY tcgen05.mma in an
+// ELECT / R2UR / BRA.U.ANY loop, ~100 clk of issue latency per instruction — measured: the issuing thread,
+// not the tensor pipe, bounded the KV tile period, profiles/r01/prefill_trace_*.json).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -108,6 +121,66 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, u
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// ---- packed fp32x2 arithmetic (FFMA2 / FADD2 on sm_100): halves the issue slots of the softmax
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+    uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+    uint64_t d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d;
+}
+__device__ __forceinline__ uint64_t fsub2(uint64_t a, uint64_t b) {
+    uint64_t d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d;
+}
+__device__ __forceinline__ uint64_t fadd2_rm(uint64_t a, uint64_t b) {   // round toward -inf
+    uint64_t d; asm("add.rm.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d;
+}
+// 2^x for a pair on the FMA pipe instead of the 16-lane/clk MUFU: Cody-Waite split with the
+// magic-number floor (x + 1.5*2^23 rounded down leaves floor(x) in the low mantissa bits), a
+// degree-3 minimax polynomial for 2^frac on [0,1) (rel. error ~1e-4, below the 2^-9 step of the
+// bf16 probabilities it feeds) and the integer part shifted into the exponent field.  x <= 127.
+__device__ __forceinline__ void exp2_poly2(uint64_t x, float& e0, float& e1) {
+    float x0, x1; f2_unpack(x, x0, x1);
+    const uint64_t xc = f2_pack(fmaxf(x0, -127.0f), fmaxf(x1, -127.0f));
+    const uint64_t magic = f2_pack(12582912.0f, 12582912.0f);
+    const uint64_t t = fadd2_rm(xc, magic);
+    const uint64_t fr = fsub2(xc, fsub2(t, magic));
+    uint64_t pl = ffma2(f2_pack(0.077119089663028717f, 0.077119089663028717f), fr,
+                        f2_pack(0.227564394474029541f, 0.227564394474029541f));
+    pl = ffma2(pl, fr, f2_pack(0.695146143436431885f, 0.695146143436431885f));
+    pl = ffma2(pl, fr, f2_pack(1.0f, 1.0f));
+    float t0, t1, p0, p1; f2_unpack(t, t0, t1); f2_unpack(pl, p0, p1);
+    e0 = __uint_as_float((__float_as_uint(t0) << 23) + __float_as_uint(p0));
+    e1 = __uint_as_float((__float_as_uint(t1) << 23) + __float_as_uint(p1));
+}
+// exp2 of 64 scores (scaled, reference max subtracted) -> packed bf16x2 probabilities + row sum.
+// NPOLY of every 4 pairs take the polynomial, the rest MUFU.EX2; two independent sum chains.
+template <int NPOLY, int HC>
+__device__ __forceinline__ float softmax_exp_tile(const uint32_t (&su)[HC], float sl2, float mr, uint32_t (&pw)[HC / 2]) {
+    const uint64_t s2 = f2_pack(sl2, sl2), m2 = f2_pack(-mr, -mr);
+    uint64_t acc0 = 0ull, acc1 = 0ull;
+#pragma unroll
+    for (int i = 0; i < HC / 2; ++i) {
+        const uint64_t x = ffma2(f2_pack(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), s2, m2);
+        float e0, e1;
+        if ((i & 3) < NPOLY) {
+            exp2_poly2(x, e0, e1);
+        } else {
+            float x0, x1; f2_unpack(x, x0, x1);
+            e0 = fast_exp2(x0); e1 = fast_exp2(x1);
+        }
+        if (i & 1) acc1 = fadd2(acc1, f2_pack(e0, e1)); else acc0 = fadd2(acc0, f2_pack(e0, e1));
+        pw[i] = pack_bf16(e0, e1);
+    }
+    float a, b; f2_unpack(fadd2(acc0, acc1), a, b);
+    return a + b;
+}
 
 // UMMA shared-memory matrix descriptor, SWIZZLE_128B, Blackwell version bit set
 // (bit layout: cute/arch/mma_sm100_desc.hpp UMMA::SmemDescriptor).
@@ -184,7 +257,14 @@ struct PrefillParams {
     int n_blocks, block_size, max_blocks_per_seq, causal;
     int64_t o_sb, o_ss, o_sh, bt_sb;
     float scale_log2;
+    long long* trace;     // debug only (b200_debug_prefill_trace): [16 events][64 tiles] clock64 stamps of CTA (0, 0, 0)
 };
+
+// Pipeline trace of ONE CTA (the heaviest: blockIdx 0,0,0): which side of each mbarrier hand-off waits.
+__device__ __forceinline__ void pf_stamp(const PrefillParams& p, bool who, int ev, int j) {
+    if (p.trace != nullptr && who && j < 64 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0)
+        p.trace[ev * 64 + j] = clock64();
+}
 
 template <int D_>
 struct PCfg {
@@ -492,7 +572,10 @@ struct PCfg2 {
 
 enum { B2_Q = 0, B2_KF = 1, B2_KE = 4, B2_VF = 7, B2_VE = 10, B2_SF = 13, B2_SE = 15, B2_PF = 17, B2_PE = 18 };
 
-template <class C>
+// SM = softmax arithmetic: 0 = scalar FFMA/MUFU/FADD with a 256-thread row-max exchange (first version);
+// k > 0 = packed fp32x2 arithmetic, 4 independent max chains, per-lane-quarter 64-thread exchange
+// barriers, and (k-1) of every 4 score pairs exponentiated by the FMA-pipe polynomial (MUFU relief).
+template <class C, int SM>
 __global__ void __launch_bounds__(C::THREADS, 1)
 prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
                          const __nv_bfloat16* __restrict__ q_rot, const __grid_constant__ PrefillParams p) {
@@ -550,11 +633,13 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
                 if (page < 0 || page >= p.n_blocks) page = 0;
                 const int tok = n0 - pe * p.block_size;
                 mbar_wait(bar(B2_KE + st), ph ^ 1u);
+                pf_stamp(p, true, 9, j);
                 mbar_expect_tx(bar(B2_KF + st), C::TILE_B);
 #pragma unroll
                 for (int sl = 0; sl < C::DSLABS; ++sl)
                     tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(B2_KF + st), sl * 64, kvh, tok, page);
                 mbar_wait(bar(B2_VE + st), ph ^ 1u);
+                pf_stamp(p, true, 10, j);
                 mbar_expect_tx(bar(B2_VF + st), C::TILE_B);
 #pragma unroll
                 for (int sl = 0; sl < C::DSLABS; ++sl)
@@ -562,42 +647,53 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
             }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer (one thread)
-        if (lane == 0) {
-            constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q (TMEM), B=K K-major
-            constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P (TMEM), B=V MN-major
-            auto issue_pv = [&](int t) {
-                const int st = t % C::KV_STAGES;
-                mbar_wait(bar(B2_VF + st), (uint32_t)(t / C::KV_STAGES) & 1u);
-                mbar_wait(bar(B2_PF), (uint32_t)t & 1u);
-                tc_fence_after();
+        // ===================================================== MMA issuer (whole warp waits, one elected lane issues)
+        constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q (TMEM), B=K K-major
+        constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P (TMEM), B=V MN-major
+        auto issue_pv = [&](int t) {
+            const int st = t % C::KV_STAGES;
+            pf_stamp(p, lane == 0, 7, t);
+            mbar_wait(bar(B2_VF + st), (uint32_t)(t / C::KV_STAGES) & 1u);
+            mbar_wait(bar(B2_PF), (uint32_t)t & 1u);
+            pf_stamp(p, lane == 0, 8, t);
+            tc_fence_after();
+            const uint32_t v_base = sV + st * C::TILE_B;
+            const uint32_t first = (t > 0) ? 1u : 0u;
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < C::BN / 16; ++k) {
-                    const uint64_t db = umma_desc_sw128(sV + st * C::TILE_B + k * 2048, C::SLAB_B, 1024);
-                    umma_bf16_ts(tmem + C::TM_O, tmem + C::TM_P + k * 8, db, IDESC_PV, (t > 0 || k > 0) ? 1u : 0u);
+                    const uint64_t db = umma_desc_sw128(v_base + k * 2048, C::SLAB_B, 1024);
+                    umma_bf16_ts(tmem + C::TM_O, tmem + C::TM_P + k * 8, db, IDESC_PV, k > 0 ? 1u : first);
                 }
                 tc_commit(bar(B2_VE + st));
                 tc_commit(bar(B2_PE));
-            };
-            mbar_wait(bar(B2_Q), 0);
+            }
+            __syncwarp();
+        };
+        mbar_wait(bar(B2_Q), 0);
+        tc_fence_after();
+        for (int j = 0; j < n_tiles; ++j) {
+            const int st = j % C::KV_STAGES;
+            const int sb = j & 1;
+            mbar_wait(bar(B2_KF + st), (uint32_t)(j / C::KV_STAGES) & 1u);
+            mbar_wait(bar(B2_SE + sb), ((uint32_t)(j >> 1) & 1u) ^ 1u);
+            pf_stamp(p, lane == 0, 6, j);
             tc_fence_after();
-            for (int j = 0; j < n_tiles; ++j) {
-                const int st = j % C::KV_STAGES;
-                const int sb = j & 1;
-                mbar_wait(bar(B2_KF + st), (uint32_t)(j / C::KV_STAGES) & 1u);
-                mbar_wait(bar(B2_SE + sb), ((uint32_t)(j >> 1) & 1u) ^ 1u);
-                tc_fence_after();
+            const uint32_t k_base = sK + st * C::TILE_B;
+            const uint32_t s_tm = tmem + (sb ? C::TM_S1 : C::TM_S0);
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
-                    const uint64_t db = umma_desc_sw128(sK + st * C::TILE_B + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
-                    umma_bf16_ts(tmem + (sb ? C::TM_S1 : C::TM_S0), tmem + C::TM_Q + k * 8, db, IDESC_QK, k > 0 ? 1u : 0u);
+                    const uint64_t db = umma_desc_sw128(k_base + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    umma_bf16_ts(s_tm, tmem + C::TM_Q + k * 8, db, IDESC_QK, k > 0 ? 1u : 0u);
                 }
                 tc_commit(bar(B2_KE + st));
                 tc_commit(bar(B2_SF + sb));
-                if (j > 0) issue_pv(j - 1);
             }
-            issue_pv(n_tiles - 1);
+            __syncwarp();
+            if (j > 0) issue_pv(j - 1);
         }
+        issue_pv(n_tiles - 1);
     } else {
         // ===================================================== softmax / correction / epilogue (8 warps)
         const int quarter = warp & 3;
@@ -639,7 +735,10 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
         for (int j = 0; j < n_tiles; ++j) {
             const int sb = j & 1;
             const int n0 = j * C::BN + half * HC;
+            const bool tr = (tid == 64);                       // first softmax thread
+            pf_stamp(p, tr, 11, j);
             mbar_wait(bar(B2_SF + sb), (uint32_t)(j >> 1) & 1u);
+            pf_stamp(p, tr, 0, j);
             tc_fence_after();
             uint32_t su[HC];
 #define SF(c) __uint_as_float(su[(c)])
@@ -656,20 +755,35 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
             }
             tc_fence_before();
             mbar_arrive(bar(B2_SE + sb));
+            pf_stamp(p, tr, 1, j);
 
-            if (n0 + HC - 1 > prefix + q0 || n0 + HC > seqlen_k) {
+            const bool masked = n0 + HC - 1 > prefix + q0 || n0 + HC > seqlen_k;   // warp-uniform
+            if (masked) {
 #pragma unroll
                 for (int c = 0; c < HC; ++c) {
                     const int tok = n0 + c;
                     if (tok > qpos || tok >= seqlen_k) su[c] = 0xff800000u;
                 }
             }
-            float mx = SF(0);
+            float mx;
+            if constexpr (SM == 0) {
+                mx = SF(0);
 #pragma unroll
-            for (int c = 1; c < HC; ++c) mx = fmaxf(mx, SF(c));
+                for (int c = 1; c < HC; ++c) mx = fmaxf(mx, SF(c));
+            } else {                                           // 4 independent chains (FMNMX3-friendly)
+                float m4[4] = {SF(0), SF(1), SF(2), SF(3)};
+#pragma unroll
+                for (int c = 4; c < HC; c += 8) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) m4[u] = fmaxf(fmaxf(m4[u], SF(c + u)), (c + 4 + u < HC) ? SF(c + 4 + u) : SF(c + u));
+                }
+                mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+            }
             xch[(j & 1) * 256 + half * 128 + row] = mx;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if constexpr (SM == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+            else asm volatile("bar.sync %0, 64;" :: "r"(1 + quarter) : "memory");   // only the 2 warps sharing these rows
             mx = fmaxf(mx, xch[(j & 1) * 256 + (half ^ 1) * 128 + row]);
+            pf_stamp(p, tr, 2, j);
             float alpha = 1.0f;
             bool grow = false;
             if (j == 0) {
@@ -683,15 +797,23 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
             const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
             float rs = 0.0f;
             uint32_t pw[HC / 2];                               // probabilities, packed bf16x2 (A operand of P.V)
+            if constexpr (SM == 0) {
 #pragma unroll
-            for (int c = 0; c < HC; c += 2) {
-                const float e0 = fast_exp2(SF(c) * sl2 - mr), e1 = fast_exp2(SF(c + 1) * sl2 - mr);
-                rs += e0 + e1;
-                pw[c >> 1] = pack_bf16(e0, e1);
+                for (int c = 0; c < HC; c += 2) {
+                    const float e0 = fast_exp2(SF(c) * sl2 - mr), e1 = fast_exp2(SF(c + 1) * sl2 - mr);
+                    rs += e0 + e1;
+                    pw[c >> 1] = pack_bf16(e0, e1);
+                }
+            } else if (masked) {                               // masked scores must give exact zeros: MUFU only
+                rs = softmax_exp_tile<0, HC>(su, sl2, mr, pw);
+            } else {
+                rs = softmax_exp_tile<SM - 1, HC>(su, sl2, mr, pw);
             }
             l += rs;
 
+            pf_stamp(p, tr, 3, j);
             mbar_wait(bar(B2_PE), ((uint32_t)j & 1u) ^ 1u);    // PV_{j-1} retired: P columns free, O stable
+            pf_stamp(p, tr, 4, j);
             tc_fence_after();
             tmem_st32(tmem + lane_sel + C::TM_P + half * (HC / 2), pw);
             if (j > 0 && __any_sync(0xffffffffu, grow)) {
@@ -709,6 +831,7 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(bar(B2_PF));
+            pf_stamp(p, tr, 5, j);
 #undef SF
         }
 
@@ -798,19 +921,19 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tk, const CU
     return 0;
 }
 
-template <class C>
+template <class C, int SM>
 static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q_rot,
                                const PrefillParams& p, cudaStream_t st) {
     static int attr_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
     if (attr_dev != dev) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_attn_tmem_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_tmem_kernel<C, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
         attr_dev = dev;
     }
     dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
-    prefill_attn_tmem_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, p);
+    prefill_attn_tmem_kernel<C, SM><<<grid, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, p);
     B200_CHECK_LAUNCH();
     return 0;
 }
@@ -818,6 +941,11 @@ static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, con
 }  // namespace b200
 
 using namespace b200;
+
+static long long* g_prefill_trace = nullptr;
+// Debug hook (not part of the operator surface): device buffer of 16*64 int64 that the next prefill launches
+// fill with clock64 stamps of CTA (0,0,0); nullptr switches tracing off.
+extern "C" void b200_debug_prefill_trace(void* dev_buf) { g_prefill_trace = (long long*)dev_buf; }
 
 extern "C" int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D) {
     if (B <= 0 || S <= 0 || Hq <= 0 || D <= 0) return -1;
@@ -882,11 +1010,20 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq; p.causal = a->causal;
     p.o_sb = a->o_stride_b; p.o_ss = a->o_stride_s; p.o_sh = a->o_stride_h; p.bt_sb = a->bt_stride_b;
     p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
+    p.trace = g_prefill_trace;
     if (a->variant == 1) {                      // operands staged in shared memory (first version, kept for A/B runs)
         if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
         return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
     }
-    if (a->variant != 0) B200_FAIL(B200_E_RANGE, "prefill: unknown variant %d", a->variant);
-    if (a->D == 128) return launch_prefill_tmem<PCfg2<128>>(tk, tv, (const __nv_bfloat16*)a->workspace, p, st);
-    return launch_prefill_tmem<PCfg2<64>>(tk, tv, (const __nv_bfloat16*)a->workspace, p, st);
+    const __nv_bfloat16* qr = (const __nv_bfloat16*)a->workspace;
+    // variant 0 = default; 2..5 pick the softmax arithmetic explicitly (A/B runs): 2 = first scalar version,
+    // 3 = packed fp32x2, 4 / 5 = packed + 25 % / 50 % of the exponentials on the FMA-pipe polynomial
+    const int sm = a->variant == 0 ? B200_PREFILL_DEFAULT_SM : a->variant - 2;
+    if (sm < 0 || sm > 3) B200_FAIL(B200_E_RANGE, "prefill: unknown variant %d", a->variant);
+#define B200_PF_DISPATCH(SMV) case SMV: \
+        if (a->D == 128) return launch_prefill_tmem<PCfg2<128>, SMV>(tk, tv, qr, p, st); \
+        return launch_prefill_tmem<PCfg2<64>, SMV>(tk, tv, qr, p, st);
+    switch (sm) { B200_PF_DISPATCH(0) B200_PF_DISPATCH(1) B200_PF_DISPATCH(2) B200_PF_DISPATCH(3) }
+#undef B200_PF_DISPATCH
+    return B200_E_RANGE;
 }

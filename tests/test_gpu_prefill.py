@@ -62,6 +62,17 @@ def test_prefill_smem_operand_variant(D, Hq, Hkv):
     check_prefill(make_paged_case(2, Hq, Hkv, D, [0, 300], S_new=390, seed=31), variant=1)
 
 
+@pytest.mark.parametrize("variant", [2, 3, 4, 5])
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
+def test_prefill_softmax_arithmetic_variants(variant, D, Hq, Hkv):
+    """variants 2..5 = the TMEM-operand kernel with each softmax arithmetic (scalar; packed fp32x2;
+    packed + 25 % / 50 % of the exponentials on the FMA-pipe polynomial): same bound against the oracle,
+    exact zeros for masked keys (ragged prefixes, partial tiles, > 2 KV ring wraps)."""
+    check_prefill(make_paged_case(2, Hq, Hkv, D, [0, 300], S_new=390, seed=41), variant=variant)
+    check_prefill(make_paged_case(1, Hq, Hkv, D, [777], S_new=1100, seed=42), variant=variant)
+    check_prefill(make_paged_case(2, Hq, Hkv, D, [5, 130], S_new=140, seed=43), causal=False, variant=variant)
+
+
 def test_prefill_interleaved_and_noncausal():
     case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=3)
     check_prefill(case, interleaved=True)

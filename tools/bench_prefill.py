@@ -60,8 +60,17 @@ def main():
             return e0.elapsed_time(e1) / iters
 
         ms = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out))
+        # the same two launches replayed from a CUDA graph: no Python / ctypes / tensor-map encode time
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out)
+        ms_graph = timeit(g.replay)
         ms1 = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=1))
-        rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
+        rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), graph_ms=round(ms_graph, 4),
+                   graph_tflops=round(flops / ms_graph / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
+        for var, key in ((2, "sm_scalar"), (3, "sm_packed"), (4, "sm_poly25"), (5, "sm_poly50")):
+            msv = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=var))
+            rec[key + "_tflops"] = round(flops / msv / 1e9, 1)
         if fa is not None:
             ms_fa = timeit(lambda: fa(q, kc, vc, k=k, v=v, rotary_cos=cos, rotary_sin=sin, cache_seqlens=lens,
                                       block_table=table, causal=True, rotary_interleaved=False))
