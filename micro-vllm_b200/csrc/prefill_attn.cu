@@ -19,6 +19,8 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <math_constants.h>
+#include <type_traits>
+#include <cstdlib>
 
 #ifndef B200_PREFILL_DEFAULT_SM
 #define B200_PREFILL_DEFAULT_SM 2   // softmax arithmetic of variant 0: packed fp32x2 + 25 % polynomial exp2 (fastest, profiles/r01/prefill_bench.json)
@@ -161,13 +163,13 @@ __device__ __forceinline__ void exp2_poly2(uint64_t x, float& e0, float& e1) {
 }
 // exp2 of 64 scores (scaled, reference max subtracted) -> packed bf16x2 probabilities + row sum.
 // NPOLY of every 4 pairs take the polynomial, the rest MUFU.EX2; two independent sum chains.
-template <int NPOLY, int HC>
-__device__ __forceinline__ float softmax_exp_tile(const uint32_t (&su)[HC], float sl2, float mr, uint32_t (&pw)[HC / 2]) {
+template <int NPOLY, int HC, int OFF = 0, int TOTAL = HC>
+__device__ __forceinline__ float softmax_exp_tile(const uint32_t (&su)[TOTAL], float sl2, float mr, uint32_t (&pw)[HC / 2]) {
     const uint64_t s2 = f2_pack(sl2, sl2), m2 = f2_pack(-mr, -mr);
     uint64_t acc0 = 0ull, acc1 = 0ull;
 #pragma unroll
     for (int i = 0; i < HC / 2; ++i) {
-        const uint64_t x = ffma2(f2_pack(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), s2, m2);
+        const uint64_t x = ffma2(f2_pack(__uint_as_float(su[OFF + 2 * i]), __uint_as_float(su[OFF + 2 * i + 1])), s2, m2);
         float e0, e1;
         if ((i & 3) < NPOLY) {
             exp2_poly2(x, e0, e1);
@@ -871,6 +873,345 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
     }
 }
 
+// ------------------------------------------------------------------ kernel 2c: two Q tiles per CTA
+// One CTA owns TWO 128-row query tiles that share every K/V tile it streams (two query heads of one KV
+// group at the same rows when G is even, else two consecutive row tiles of one head): K/V traffic from L2
+// halves, and the tensor pipe works on one tile's GEMMs while the other tile's softmax runs (ping-pong).
+//   TMEM   : S_A | S_B | O_A | O_B  (4 x 128 columns).  The probabilities overwrite the scores in place:
+//            P_x = packed bf16x2 in score columns 0..31 (keys 0..63) and 64..95 (keys 64..127) of S_x,
+//            consumed as the TMEM A operand of P.V.
+//            No "S free" barrier is needed — Q.K^T of tile j+1 is issued after P.V of tile j by the same
+//            thread, and tcgen05.mma executes in issue order.
+//   smem   : Q_A, Q_B (TMA, once), 2-stage K ring, 2-stage V ring (128B-swizzled UMMA tiles).
+//   warps  : 0 = TMA producer, 1 = MMA issuer, 2-9 = softmax of tile A, 10-17 = softmax of tile B; two
+//            threads per query row (64 key columns each, row max exchanged through shared memory behind a
+//            64-thread named barrier), two passes over the columns in 32-column chunks of tcgen05.ld (max,
+//            then exp / pack / tcgen05.st into the thread's OWN score columns): <= 96 registers at 18 warps.
+template <int D_>
+struct PCfg3 {
+    static constexpr int D = D_;
+    static constexpr int BM = 128, BN = 128;
+    static constexpr int SLAB_B = 128 * 128;
+    static constexpr int DSLABS = D / 64;
+    static constexpr int TILE_B = DSLABS * SLAB_B;
+    static constexpr int KV_STAGES = 2;
+    static constexpr int OFF_Q = 0;                                  // Q_A, Q_B
+    static constexpr int OFF_K = OFF_Q + 2 * TILE_B;
+    static constexpr int OFF_V = OFF_K + KV_STAGES * TILE_B;
+    static constexpr int OFF_BAR = OFF_V + KV_STAGES * TILE_B;
+    static constexpr int NBARS = 16;
+    static constexpr int OFF_XCH = OFF_BAR + NBARS * 8 + 16;         // row max / row sum exchange [2 tiles][2][2][128] f32
+    static constexpr int SMEM = OFF_XCH + 2 * 2 * 2 * 128 * 4 + 1024;
+    static constexpr int GROUP_THREADS = 256;                        // two threads per query row
+    static constexpr int THREADS = 64 + 2 * GROUP_THREADS;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int TM_S = 0, TM_O = 256;                       // + 128 * tile
+};
+
+enum { B3_Q = 0, B3_KF = 1, B3_KE = 3, B3_VF = 5, B3_VE = 7, B3_SF = 9, B3_PF = 11, B3_PD = 13 };
+
+struct PairParams {
+    PrefillParams p;
+    int pair_heads;        // 1: tiles = heads (2*y, 2*y+1) at rows x*128;  0: tiles = rows (2*x, 2*x+1)*128 of head y
+};
+
+template <class C, int SM>
+__global__ void __launch_bounds__(C::THREADS, 1)
+prefill_attn_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                         const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ PairParams pp) {
+    constexpr int D = C::D;
+    const PrefillParams& p = pp.p;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_u32 = smem_u32(smem_raw);
+    const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw_u32);
+    const uint32_t sQ = base + C::OFF_Q, sK = base + C::OFF_K, sV = base + C::OFF_V;
+    const uint32_t bars = base + C::OFF_BAR;
+    auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
+    volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int xt = (int)gridDim.x - 1 - (int)blockIdx.x;            // heaviest causal tiles first
+    const int b = blockIdx.z;
+    // tile t in {0,1}: head hq_t, first row q0_t
+    const int hq0 = pp.pair_heads ? 2 * (int)blockIdx.y : (int)blockIdx.y;
+    const int hq1 = pp.pair_heads ? hq0 + 1 : hq0;
+    const int q00 = pp.pair_heads ? xt * C::BM : 2 * xt * C::BM;
+    const int q01 = pp.pair_heads ? q00 : q00 + C::BM;
+    const int q01_load = (q01 < p.S) ? q01 : q00;                    // a dead second tile re-reads tile 0 (never stored)
+    const int kvh = hq0 / p.G;                                        // == hq1 / G (G even when heads are paired)
+    const int prefix = __ldg(p.seqlens + b);
+    const int seqlen_k = prefix + p.S;
+    const int kv_end = p.causal ? min(seqlen_k, prefix + q01 + C::BM) : seqlen_k;
+    const int n_tiles = (kv_end + C::BN - 1) / C::BN;
+
+    if (tid == 0) {
+        mbar_init(bar(B3_Q), 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bar(B3_KF + s), 1); mbar_init(bar(B3_KE + s), 1);
+            mbar_init(bar(B3_VF + s), 1); mbar_init(bar(B3_VE + s), 1);
+            mbar_init(bar(B3_SF + s), 1); mbar_init(bar(B3_PF + s), C::GROUP_THREADS); mbar_init(bar(B3_PD + s), 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32((const void*)s_tmem)), "r"((uint32_t)C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer (warp-uniform loop, elected lane issues)
+        if (elect_one()) {
+            mbar_expect_tx(bar(B3_Q), 2 * C::TILE_B);
+#pragma unroll
+            for (int sl = 0; sl < C::DSLABS; ++sl) {
+                tma_load_4d(sQ + sl * C::SLAB_B, &tm_q, bar(B3_Q), sl * 64, hq0, q00, b);
+                tma_load_4d(sQ + C::TILE_B + sl * C::SLAB_B, &tm_q, bar(B3_Q), sl * 64, hq1, q01_load, b);
+            }
+        }
+        __syncwarp();
+        const int32_t* bt = p.block_table + (int64_t)b * p.bt_sb;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int st = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            const int n0 = j * C::BN;
+            const int pe = n0 / p.block_size;
+            int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : 0;
+            if (page < 0 || page >= p.n_blocks) page = 0;          // memory safety; tokens are masked or undefined
+            const int tok = n0 - pe * p.block_size;
+            mbar_wait(bar(B3_KE + st), ph ^ 1u);
+            pf_stamp(p, lane == 0, 9, j);
+            if (elect_one()) {
+                mbar_expect_tx(bar(B3_KF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(B3_KF + st), sl * 64, kvh, tok, page);
+            }
+            __syncwarp();
+            mbar_wait(bar(B3_VE + st), ph ^ 1u);
+            pf_stamp(p, lane == 0, 10, j);
+            if (elect_one()) {
+                mbar_expect_tx(bar(B3_VF + st), C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl)
+                    tma_load_4d(sV + st * C::TILE_B + sl * C::SLAB_B, &tm_v, bar(B3_VF + st), sl * 64, kvh, tok, page);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer (whole warp waits, one elected lane issues)
+        constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q K-major (smem), B=K K-major
+        constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P (TMEM), B=V MN-major
+        auto issue_qk = [&](int t, int j) {                 // S_t = Q_t . K_j^T ; K_j must have landed
+            const uint32_t k_base = sK + (j & 1) * C::TILE_B;
+            const uint32_t q_base = sQ + t * C::TILE_B;
+            const uint32_t s_tm = tmem + C::TM_S + t * 128;
+            pf_stamp(p, lane == 0 && t == 0, 6, j);
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t da = umma_desc_sw128(q_base + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    const uint64_t db = umma_desc_sw128(k_base + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    umma_bf16(s_tm, da, db, IDESC_QK, k > 0 ? 1u : 0u);
+                }
+                tc_commit(bar(B3_SF + t));
+                if (t == 1) tc_commit(bar(B3_KE + (j & 1)));          // both tiles have consumed K_j
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int t, int j) {                 // O_t += P_t . V_j ; waits for tile t's softmax
+            pf_stamp(p, lane == 0 && t == 0, 7, j);
+            mbar_wait(bar(B3_PF + t), (uint32_t)j & 1u);
+            pf_stamp(p, lane == 0 && t == 0, 8, j);
+            tc_fence_after();
+            const uint32_t v_base = sV + (j & 1) * C::TILE_B;
+            const uint32_t p_tm = tmem + C::TM_S + t * 128;            // P overwrote S in place
+            const uint32_t o_tm = tmem + C::TM_O + t * 128;
+            const uint32_t first = (j > 0) ? 1u : 0u;
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < C::BN / 16; ++k) {
+                    const uint64_t db = umma_desc_sw128(v_base + k * 2048, C::SLAB_B, 1024);
+                    // P words of tokens 0..63 sit in score columns 0..31, tokens 64..127 in columns 64..95
+                    umma_bf16_ts(o_tm, p_tm + (k < 4 ? k * 8 : 64 + (k - 4) * 8), db, IDESC_PV, k > 0 ? 1u : first);
+                }
+                tc_commit(bar(B3_PD + t));
+                if (t == 1) tc_commit(bar(B3_VE + (j & 1)));          // both tiles have consumed V_j
+            }
+            __syncwarp();
+        };
+        mbar_wait(bar(B3_Q), 0);
+        mbar_wait(bar(B3_KF), 0);
+        tc_fence_after();
+        issue_qk(0, 0);
+        issue_qk(1, 0);
+        for (int j = 0; j < n_tiles; ++j) {
+            const bool more = (j + 1 < n_tiles);
+            mbar_wait(bar(B3_VF + (j & 1)), (uint32_t)(j >> 1) & 1u);
+            if (more) mbar_wait(bar(B3_KF + ((j + 1) & 1)), (uint32_t)((j + 1) >> 1) & 1u);
+            issue_pv(0, j);
+            if (more) issue_qk(0, j + 1);
+            issue_pv(1, j);
+            if (more) issue_qk(1, j + 1);
+        }
+    } else {
+        // ===================================================== softmax / correction / epilogue
+        // 16 warps: tile t = (w >> 3), column half = (w >> 2) & 1, TMEM lane quarter = warp & 3.  TWO threads per
+        // query row (64 key columns each) keep four warps on every scheduler, so one warp's MUFU / FMA / ALU
+        // stalls are filled by the others (a lone warp per row serialises the three pipes: measured 1780 clk
+        // for the exp pass of 128 columns against 1100 clk for two lock-stepped 64-column warps).
+        const int w = warp - 2;
+        const int t = w >> 3;                                  // which Q tile
+        const int half = (w >> 2) & 1;                         // which 64 key columns / which half of D
+        const int quarter = warp & 3;                          // TMEM lane quarter this warp may access
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const int hq = t ? hq1 : hq0;
+        const int q0 = t ? q01 : q00;
+        const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
+        const float sl2 = p.scale_log2;
+        constexpr int HC = C::BN / 2, HD = D / 2;
+        const uint32_t ts = tmem + lane_sel + C::TM_S + t * 128 + half * HC;     // my 64 score columns; my P words
+        const uint32_t to = tmem + lane_sel + C::TM_O + t * 128 + half * HD;     // overwrite their first 32
+        constexpr int NPOLY = SM > 0 ? SM - 1 : 0;
+        volatile float* xch = reinterpret_cast<volatile float*>(smem + C::OFF_XCH) + t * 512;   // [parity][half][row]
+        const int pair_bar = 1 + t * 4 + quarter;              // named barrier of the 2 warps that share these rows
+        float m_ref = -CUDART_INF_F, l = 0.0f;
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int n0 = j * C::BN + half * HC;
+            const bool tr = (tid == 64);
+            pf_stamp(p, tr, 11, j);
+            mbar_wait(bar(B3_SF + t), (uint32_t)j & 1u);
+            pf_stamp(p, tr, 0, j);
+            pf_stamp(p, tr, 1, j);
+            tc_fence_after();
+            const bool masked = (n0 + HC - 1 > prefix + q0) || (n0 + HC > seqlen_k);   // warp-uniform
+            // ---- pass 1: maximum of my 64 columns, then across the two halves of the row
+            float m4[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+#pragma unroll
+            for (int c = 0; c < HC / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld32(ts + c * 32, r);
+                tmem_wait_ld();
+                if (masked) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int tok = n0 + c * 32 + i;
+                        if (tok > qpos || tok >= seqlen_k) r[i] = 0xff800000u;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        m4[u] = fmaxf(fmaxf(m4[u], __uint_as_float(r[i + u])), __uint_as_float(r[i + 4 + u]));
+                }
+            }
+            float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+            xch[(j & 1) * 256 + half * 128 + row] = mx;
+            asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+            mx = fmaxf(mx, xch[(j & 1) * 256 + (half ^ 1) * 128 + row]);
+            pf_stamp(p, tr, 2, j);
+            // lazy rescale: keep the old reference max unless it is off by more than 2^8
+            // (both threads of a row take the same decision from the same numbers)
+            float alpha = 1.0f;
+            bool grow = false;
+            if (j == 0) {
+                m_ref = mx;
+            } else if ((mx - m_ref) * sl2 > 8.0f) {
+                alpha = fast_exp2((m_ref - mx) * sl2);
+                m_ref = mx;
+                l *= alpha;
+                grow = true;
+            }
+            if (j > 0 && __any_sync(0xffffffffu, grow)) {      // warp-uniform: tcgen05.ld/st are warp-collective
+                mbar_wait(bar(B3_PD + t), (uint32_t)(j - 1) & 1u);   // P.V of tile j-1 retired: O stable
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < HD / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(to + c * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                    tmem_st32(to + c * 32, r);
+                }
+            }
+            const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
+            // ---- pass 2: probabilities over my own score columns (16 packed words per 32 scores land behind my
+            //      own read frontier: no other thread reads or writes these columns)
+            float rs = 0.0f;
+#pragma unroll
+            for (int c = 0; c < HC / 32; ++c) {
+                uint32_t r[32];
+                uint32_t pw[16];
+                tmem_ld32(ts + c * 32, r);
+                tmem_wait_ld();
+                if (masked) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int tok = n0 + c * 32 + i;
+                        if (tok > qpos || tok >= seqlen_k) r[i] = 0xff800000u;
+                    }
+                    rs += softmax_exp_tile<0, 32>(r, sl2, mr, pw);       // exact zeros for masked keys
+                } else {
+                    rs += softmax_exp_tile<NPOLY, 32>(r, sl2, mr, pw);
+                }
+                tmem_st16(ts + c * 16, pw);
+            }
+            l += rs;
+            pf_stamp(p, tr, 3, j);
+            pf_stamp(p, tr, 4, j);
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar(B3_PF + t));
+            pf_stamp(p, tr, 5, j);
+        }
+
+        // epilogue: row sum across the two halves, O / l -> bf16 -> global (each thread half of D)
+        asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+        xch[half * 128 + row] = l;
+        asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+        l += xch[(half ^ 1) * 128 + row];
+        mbar_wait(bar(B3_PD + t), (uint32_t)(n_tiles - 1) & 1u);
+        tc_fence_after();
+        const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
+        const bool live = (q0 + row) < p.S;
+        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh + half * HD;
+#pragma unroll
+        for (int c = 0; c < HD / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(to + c * 32, r);
+            tmem_wait_ld();
+            if (live) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 v;
+                    v.x = pack_bf16(__uint_as_float(r[i * 8 + 0]) * inv, __uint_as_float(r[i * 8 + 1]) * inv);
+                    v.y = pack_bf16(__uint_as_float(r[i * 8 + 2]) * inv, __uint_as_float(r[i * 8 + 3]) * inv);
+                    v.z = pack_bf16(__uint_as_float(r[i * 8 + 4]) * inv, __uint_as_float(r[i * 8 + 5]) * inv);
+                    v.w = pack_bf16(__uint_as_float(r[i * 8 + 6]) * inv, __uint_as_float(r[i * 8 + 7]) * inv);
+                    *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -934,6 +1275,28 @@ static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, con
     }
     dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
     prefill_attn_tmem_kernel<C, SM><<<grid, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, p);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+template <class C, int SM>
+static int launch_prefill_pair(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                               const PrefillParams& p, cudaStream_t st) {
+    static int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_pair_kernel<C, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
+        attr_dev = dev;
+    }
+    PairParams pp;
+    pp.p = p;
+    pp.pair_heads = (p.G % 2 == 0) ? 1 : 0;
+    const unsigned q_tiles = (unsigned)((p.S + C::BM - 1) / C::BM);
+    dim3 grid = pp.pair_heads ? dim3(q_tiles, (unsigned)p.Hq / 2, (unsigned)p.B)
+                              : dim3((q_tiles + 1) / 2, (unsigned)p.Hq, (unsigned)p.B);
+    prefill_attn_pair_kernel<C, SM><<<grid, C::THREADS, C::SMEM, st>>>(tq, tk, tv, pp);
     B200_CHECK_LAUNCH();
     return 0;
 }
@@ -1015,10 +1378,28 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
         if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
         return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
     }
+    int variant = a->variant;
+    if (variant == 0) {
+        // default: two Q tiles per CTA (half the K/V traffic, half the prologues per unit of work, ping-pong)
+        // whenever that grid still fills the GPU; the one-tile kernel for small grids and for head_dim 64
+        // (measured, profiles/r01/prefill_bench.json)
+        static int n_sm = 0;
+        if (n_sm == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+        const long long q_tiles = (a->S + 127) / 128;
+        const long long pair_ctas = ((p.G % 2 == 0) ? q_tiles * (a->Hq / 2) : ((q_tiles + 1) / 2) * a->Hq) * a->B;
+        if (a->D == 128 && pair_ctas >= n_sm) variant = 6;
+    }
+    if (variant >= 6 && variant <= 8) {   // two Q tiles per CTA (ping-pong); 6 / 7 / 8 = 25 % / 0 % / 50 % polynomial exp2
+#define B200_PP_DISPATCH(V, SMV) if (variant == V) { \
+        if (a->D == 128) return launch_prefill_pair<PCfg3<128>, SMV>(tq, tk, tv, p, st); \
+        return launch_prefill_pair<PCfg3<64>, SMV>(tq, tk, tv, p, st); }
+        B200_PP_DISPATCH(6, 2) B200_PP_DISPATCH(7, 1) B200_PP_DISPATCH(8, 3)
+#undef B200_PP_DISPATCH
+    }
     const __nv_bfloat16* qr = (const __nv_bfloat16*)a->workspace;
     // variant 0 = default; 2..5 pick the softmax arithmetic explicitly (A/B runs): 2 = first scalar version,
     // 3 = packed fp32x2, 4 / 5 = packed + 25 % / 50 % of the exponentials on the FMA-pipe polynomial
-    const int sm = a->variant == 0 ? B200_PREFILL_DEFAULT_SM : a->variant - 2;
+    const int sm = variant == 0 ? B200_PREFILL_DEFAULT_SM : variant - 2;
     if (sm < 0 || sm > 3) B200_FAIL(B200_E_RANGE, "prefill: unknown variant %d", a->variant);
 #define B200_PF_DISPATCH(SMV) case SMV: \
         if (a->D == 128) return launch_prefill_tmem<PCfg2<128>, SMV>(tk, tv, qr, p, st); \

@@ -73,6 +73,36 @@ def test_prefill_softmax_arithmetic_variants(variant, D, Hq, Hkv):
     check_prefill(make_paged_case(2, Hq, Hkv, D, [5, 130], S_new=140, seed=43), causal=False, variant=variant)
 
 
+PAIR_CASES = [  # B, S, Hq, Hkv, D, prefixes
+    (1, 128, 4, 4, 128, [0]),            # G = 1 (odd): two consecutive row tiles per CTA, second one dead
+    (2, 128, 8, 2, 128, [0, 0]),         # G = 4 (even): two heads per CTA
+    (2, 100, 4, 2, 128, [0, 57]),        # partial tile
+    (1, 1, 4, 4, 128, [0]),
+    (3, 129, 14, 2, 64, [0, 1, 255]),    # G = 7, D = 64, odd number of row tiles
+    (1, 512, 28, 4, 128, [0]),           # Qwen2.5-7B heads, 4 row tiles -> 2 CTAs per head
+    (2, 300, 32, 8, 128, [0, 300]),      # Llama-3-8B heads on a cached prefix
+    (1, 1100, 8, 2, 128, [777]),         # > 2 K/V ring wraps, ragged prefix
+    (2, 390, 14, 2, 64, [0, 300]),
+    (1, 700, 6, 6, 128, [131]),          # MHA, odd tile count, prefix not tile aligned
+]
+
+
+@pytest.mark.parametrize("variant", [6, 7, 8])
+@pytest.mark.parametrize("B,S,Hq,Hkv,D,prefixes", PAIR_CASES)
+def test_prefill_two_tiles_per_cta(variant, B, S, Hq, Hkv, D, prefixes):
+    """variants 6..8 = two 128-row query tiles per CTA sharing each K/V tile (ping-pong), probabilities
+    written over the scores in tensor memory; head pairs when G is even, row-tile pairs otherwise."""
+    check_prefill(make_paged_case(B, Hq, Hkv, D, prefixes, S_new=S, seed=S + Hq + variant), variant=variant)
+
+
+@pytest.mark.parametrize("variant", [6, 8])
+def test_prefill_two_tiles_long_and_noncausal(variant):
+    check_prefill(make_paged_case(1, 8, 2, 128, [0], S_new=2048, seed=51), variant=variant)
+    check_prefill(make_paged_case(1, 7, 1, 128, [300], S_new=1500, seed=52), variant=variant)
+    check_prefill(make_paged_case(2, 8, 4, 128, [5, 130], S_new=140, seed=53), causal=False, variant=variant)
+    check_prefill(make_paged_case(2, 3, 3, 64, [5, 130], S_new=260, seed=54), causal=False, variant=variant)
+
+
 def test_prefill_interleaved_and_noncausal():
     case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=3)
     check_prefill(case, interleaved=True)

@@ -68,7 +68,7 @@ def main():
         ms1 = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=1))
         rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), graph_ms=round(ms_graph, 4),
                    graph_tflops=round(flops / ms_graph / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
-        for var, key in ((2, "sm_scalar"), (3, "sm_packed"), (4, "sm_poly25"), (5, "sm_poly50")):
+        for var, key in ((3, "sm_packed"), (4, "sm_poly25"), (5, "sm_poly50"), (6, "pair_poly25"), (7, "pair_packed"), (8, "pair_poly50")):
             msv = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=var))
             rec[key + "_tflops"] = round(flops / msv / 1e9, 1)
         if fa is not None:
