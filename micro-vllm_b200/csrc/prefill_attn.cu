@@ -259,12 +259,13 @@ struct PrefillParams {
     int n_blocks, block_size, max_blocks_per_seq, causal;
     int64_t o_sb, o_ss, o_sh, bt_sb;
     float scale_log2;
+    int nx, ny;           // 1-D grids: blockIdx.x = (x * B + b) * ny + y, x = causal weight rank (0 = heaviest row tile)
     long long* trace;     // debug only (b200_debug_prefill_trace): [16 events][64 tiles] clock64 stamps of CTA (0, 0, 0)
 };
 
 // Pipeline trace of ONE CTA (the heaviest: blockIdx 0,0,0): which side of each mbarrier hand-off waits.
 __device__ __forceinline__ void pf_stamp(const PrefillParams& p, bool who, int ev, int j) {
-    if (p.trace != nullptr && who && j < 64 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0)
+    if (p.trace != nullptr && who && j < 64 && blockIdx.x == 0)
         p.trace[ev * 64 + j] = clock64();
 }
 
@@ -592,9 +593,13 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
     volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int qt = (int)gridDim.x - 1 - (int)blockIdx.x;
+    // longest-processing-time-first order over the WHOLE grid: every (head, batch) CTA of the heaviest causal
+    // row tile is dispatched before any CTA of the next one, so the tail of the launch is made of short CTAs
+    const int hq = (int)blockIdx.x % p.ny;
+    const int xb = (int)blockIdx.x / p.ny;
+    const int b = xb % p.B;
+    const int qt = p.nx - 1 - xb / p.B;
     const int q0 = qt * C::BM;
-    const int hq = blockIdx.y, b = blockIdx.z;
     const int kvh = hq / p.G;
     const int prefix = __ldg(p.seqlens + b);
     const int seqlen_k = prefix + p.S;
@@ -931,10 +936,13 @@ prefill_attn_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int xt = (int)gridDim.x - 1 - (int)blockIdx.x;            // heaviest causal tiles first
-    const int b = blockIdx.z;
+    // longest-processing-time-first order over the whole grid (see prefill_attn_tmem_kernel)
+    const int by = (int)blockIdx.x % p.ny;
+    const int xb = (int)blockIdx.x / p.ny;
+    const int b = xb % p.B;
+    const int xt = p.nx - 1 - xb / p.B;
     // tile t in {0,1}: head hq_t, first row q0_t
-    const int hq0 = pp.pair_heads ? 2 * (int)blockIdx.y : (int)blockIdx.y;
+    const int hq0 = pp.pair_heads ? 2 * by : by;
     const int hq1 = pp.pair_heads ? hq0 + 1 : hq0;
     const int q00 = pp.pair_heads ? xt * C::BM : 2 * xt * C::BM;
     const int q01 = pp.pair_heads ? q00 : q00 + C::BM;
@@ -1273,8 +1281,12 @@ static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, con
         if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
         attr_dev = dev;
     }
-    dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
-    prefill_attn_tmem_kernel<C, SM><<<grid, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, p);
+    PrefillParams pl = p;
+    pl.nx = (p.S + C::BM - 1) / C::BM;
+    pl.ny = p.Hq;
+    const long long n_ctas = (long long)pl.nx * pl.ny * p.B;
+    if (n_ctas > 0x7fffffffLL) { set_error("prefill: grid too large"); return B200_E_RANGE; }
+    prefill_attn_tmem_kernel<C, SM><<<(unsigned)n_ctas, C::THREADS, C::SMEM, st>>>(tk, tv, q_rot, pl);
     B200_CHECK_LAUNCH();
     return 0;
 }
@@ -1293,10 +1305,12 @@ static int launch_prefill_pair(const CUtensorMap& tq, const CUtensorMap& tk, con
     PairParams pp;
     pp.p = p;
     pp.pair_heads = (p.G % 2 == 0) ? 1 : 0;
-    const unsigned q_tiles = (unsigned)((p.S + C::BM - 1) / C::BM);
-    dim3 grid = pp.pair_heads ? dim3(q_tiles, (unsigned)p.Hq / 2, (unsigned)p.B)
-                              : dim3((q_tiles + 1) / 2, (unsigned)p.Hq, (unsigned)p.B);
-    prefill_attn_pair_kernel<C, SM><<<grid, C::THREADS, C::SMEM, st>>>(tq, tk, tv, pp);
+    const int q_tiles = (p.S + C::BM - 1) / C::BM;
+    pp.p.nx = pp.pair_heads ? q_tiles : (q_tiles + 1) / 2;
+    pp.p.ny = pp.pair_heads ? p.Hq / 2 : p.Hq;
+    const long long n_ctas = (long long)pp.p.nx * pp.p.ny * p.B;
+    if (n_ctas > 0x7fffffffLL) { set_error("prefill: grid too large"); return B200_E_RANGE; }
+    prefill_attn_pair_kernel<C, SM><<<(unsigned)n_ctas, C::THREADS, C::SMEM, st>>>(tq, tk, tv, pp);
     B200_CHECK_LAUNCH();
     return 0;
 }
@@ -1373,6 +1387,7 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq; p.causal = a->causal;
     p.o_sb = a->o_stride_b; p.o_ss = a->o_stride_s; p.o_sh = a->o_stride_h; p.bt_sb = a->bt_stride_b;
     p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
+    p.nx = p.ny = 0;
     p.trace = g_prefill_trace;
     if (a->variant == 1) {                      // operands staged in shared memory (first version, kept for A/B runs)
         if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
@@ -1381,13 +1396,13 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     int variant = a->variant;
     if (variant == 0) {
         // default: two Q tiles per CTA (half the K/V traffic, half the prologues per unit of work, ping-pong)
-        // whenever that grid still fills the GPU; the one-tile kernel for small grids and for head_dim 64
+        // whenever that grid still fills the GPU; the one-tile kernel for small grids
         // (measured, profiles/r01/prefill_bench.json)
         static int n_sm = 0;
         if (n_sm == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
         const long long q_tiles = (a->S + 127) / 128;
         const long long pair_ctas = ((p.G % 2 == 0) ? q_tiles * (a->Hq / 2) : ((q_tiles + 1) / 2) * a->Hq) * a->B;
-        if (a->D == 128 && pair_ctas >= n_sm) variant = 6;
+        if (pair_ctas >= n_sm) variant = 6;
     }
     if (variant >= 6 && variant <= 8) {   // two Q tiles per CTA (ping-pong); 6 / 7 / 8 = 25 % / 0 % / 50 % polynomial exp2
 #define B200_PP_DISPATCH(V, SMV) if (variant == V) { \
