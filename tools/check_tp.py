@@ -87,7 +87,7 @@ def main():
            "timeout_flag": err}
     if rank == 0:
         print(json.dumps(res), flush=True)
-    ok = same and rel0 < 0.02 and err == 0
+    ok = same and rel0 < 0.03 and err == 0      # bf16 rounding-order noise of a 4-layer stack is 1-2 % rms
     # graphs that captured NCCL kernels must be gone before the communicator is destroyed (else destroy waits forever)
     del runner, mgr
     import gc
