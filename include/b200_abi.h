@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 9
+#define B200_ABI_VERSION 10
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -99,6 +99,25 @@ int b200_store_kvcache(const void* key, const void* value,
                        int64_t kt, int64_t kh, int64_t vt, int64_t vh,
                        int64_t n_blocks, int64_t block_size,
                        int64_t cb, int64_t cs, int64_t ch,
+                       void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Greedy token selection — replaces core/layer/sampler.py:21-43 evaluated at
+ * top_k = 1 (torch.topk(logits / temp, 1): the index of the row maximum; the
+ * softmax / top-p / multinomial over one candidate are the identity), called
+ * from core/engine.py:276-280.  Runs as the last launch of the captured decode
+ * step so the ids never leave the device.
+ *   out_ids[r] = FIRST index of the maximum of logits[r, 0..vocab)   (int64)
+ * logits [rows, vocab] bf16 (B200_DT_BF16) or fp32 (B200_DT_F32), row stride in
+ * elements, rows <= 65535.  NaN (sign clear) orders above +inf like torch.topk.
+ * workspace: b200_greedy_argmax_workspace_bytes(rows) bytes, 8-byte aligned,
+ * ZERO-FILLED ONCE by the caller; the kernel leaves it zeroed (replay safe).
+ * ------------------------------------------------------------------------ */
+int64_t b200_greedy_argmax_workspace_bytes(int64_t rows);
+int b200_greedy_argmax(const void* logits, int logits_dtype,
+                       int64_t rows, int64_t vocab, int64_t stride,
+                       int64_t* out_ids,
+                       void* workspace, int64_t workspace_bytes,
                        void* stream);
 
 /* ------------------------------------------------------------------------ *

@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "greedy_argmax", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
 ]
 
 
@@ -305,3 +305,21 @@ def paged_attn_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
     check(lib.b200_paged_attn_prefill(C.byref(a), _stream()), "b200_paged_attn_prefill")
     return out
+
+
+# ------------------------------------------------------------------ greedy sampling
+def greedy_argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[r] = first index of max(logits[r, :]) as int64 (core/layer/sampler.py:21-43 at top_k = 1).
+    logits [rows, vocab] bf16 or fp32, last dim contiguous; capturable (scratch is per device/stream,
+    zeroed once, left zeroed by the kernel)."""
+    _req_cuda(logits, out)
+    assert logits.dim() == 2 and logits.stride(1) == 1, "greedy_argmax: [rows, vocab], last dim contiguous"
+    assert logits.dtype in (torch.bfloat16, torch.float32), "greedy_argmax: bf16 / fp32 logits"
+    rows, vocab = logits.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() >= rows
+    ws = _workspace(logits.device, int(lib.b200_greedy_argmax_workspace_bytes(max(rows, 1))), "argmax")
+    check(lib.b200_greedy_argmax(logits.data_ptr(), _wdt(logits), rows, vocab, logits.stride(0) if rows > 1 else max(logits.stride(0), vocab),
+                                 out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "b200_greedy_argmax")
+    return out[:rows]

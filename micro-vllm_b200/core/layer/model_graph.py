@@ -114,6 +114,7 @@ class ModelGraphRunner:
         qkv_dim, o_in = blk.attn._qkv_w.shape[1], blk.attn._o.shape[0]
         gu_dim = blk.mlp._gu.shape[1]
         self._input_ids = torch.empty(mb, dtype=torch.long, device=dev)
+        self._next_ids = torch.zeros(mb, dtype=torch.long, device=dev)       # greedy ids (capture(greedy=True))
         self._logits = torch.empty(mb, self.vocab_size, dtype=dt, device=dev)
         self._normed = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
         self._qkv = torch.empty((mb, qkv_dim), dtype=dt, device=dev)
@@ -223,12 +224,17 @@ class ModelGraphRunner:
     # on uniform batches the split grid stays ~20 % faster, so it remains the default).
     RAGGED_RATIO = 1.5
 
-    def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32], ragged: bool = False):
+    def capture(self, cache_manager, batch_sizes: List[int] = [1, 2, 4, 8, 16, 32], ragged: bool = False,
+                greedy: bool = False):
         """3 eager warm-ups then ``torch.cuda.graph`` per batch size (reference :225-253).  ``ragged`` also
         captures, for every batch size > 1, a second graph whose attention uses the balanced schedule;
-        ``forward`` replays it when the cache manager reports a ragged batch."""
+        ``forward`` replays it when the cache manager reports a ragged batch.  ``greedy`` appends the row
+        arg-max of the logits (``b200_greedy_argmax``: the reference sampler at top_k = 1, sampler.py:21-43)
+        as the last launch of every graph, so ``forward_greedy`` returns token ids without the logits
+        leaving the device."""
         if self._is_graph_ready:
             return
+        self._greedy_in_graph = bool(greedy)
         for bs in batch_sizes:
             for balanced in ((False, True) if ragged and bs > 1 and bs <= 512 else (False,)):
                 dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
@@ -240,6 +246,8 @@ class ModelGraphRunner:
                 with torch.no_grad(), torch.cuda.graph(g):
                     self._logits[:bs] = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True,
                                                     balanced=balanced)
+                    if greedy:
+                        b200ops.greedy_argmax(self._logits[:bs], self._next_ids[:bs])
                 if balanced:
                     self._graphs_balanced[bs] = g
                 else:
@@ -255,9 +263,18 @@ class ModelGraphRunner:
         self._input_ids[:batch_size] = input_ids
         ragged = self._is_ragged(cache_manager, batch_size)
         g = (self._graphs_balanced.get(batch_size) if ragged else None) or self._graphs.get(batch_size)
+        self._replayed = g is not None
         if g is None:
             with torch.no_grad():
                 return self.decode(input_ids, batch_size, cache_manager, use_graph_cache=True,
                                    balanced=ragged and batch_size <= 512)
         g.replay()
         return self._logits[:batch_size]
+
+    def forward_greedy(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
+        """One decode step returning the greedy next-token ids ``[batch_size]`` int64 (a view of a static
+        buffer).  Inside the graph when captured with ``greedy=True``; otherwise one extra launch."""
+        logits = self.forward(input_ids, cache_manager, batch_size)
+        if not (self._replayed and getattr(self, "_greedy_in_graph", False)):
+            b200ops.greedy_argmax(logits, self._next_ids[:batch_size])
+        return self._next_ids[:batch_size]

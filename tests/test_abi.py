@@ -51,6 +51,13 @@ def test_argument_errors_without_device():
     assert lib.b200_store_kvcache(None, None, None, None, None, 1, 1, 8, 8, 8, 8, 8, 1, 256, 8, 8, 8, None) == _lib.E_NULL
     assert lib.b200_paged_attn_decode(None, None) == _lib.E_NULL
     assert lib.b200_paged_attn_prefill(None, None) == _lib.E_NULL
+    assert lib.b200_greedy_argmax(None, 0, 1, 8, 8, None, None, 0, None) == _lib.E_NULL
+    assert lib.b200_greedy_argmax(0x1000, 0, 1, 8, 4, 0x1000, None, 0, None) == _lib.E_RANGE          # stride < vocab
+    assert lib.b200_greedy_argmax(0x1000, 7, 1, 8, 8, 0x1000, None, 0, None) == _lib.E_UNSUPPORTED    # dtype
+    assert lib.b200_greedy_argmax(0x1000, 0, 4, 100000, 100000, 0x1000, None, 0, None) == _lib.E_NULL  # scratch needed
+    assert lib.b200_greedy_argmax(0x1000, 0, 4, 100000, 100000, 0x1000, 0x1000, 8, None) == _lib.E_RANGE
+    assert lib.b200_greedy_argmax(0x1000, 0, 0, 100000, 100000, 0x1000, None, 0, None) == 0            # no rows: no-op
+    assert lib.b200_greedy_argmax_workspace_bytes(32) == 512
     a = _lib.DecodeArgs()
     for f in ("q", "k_cache", "v_cache", "cache_seqlens", "block_table", "out"):
         setattr(a, f, 0x1000)
