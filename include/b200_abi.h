@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 10
+#define B200_ABI_VERSION 11
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -119,6 +119,31 @@ int b200_greedy_argmax(const void* logits, int logits_dtype,
                        int64_t* out_ids,
                        void* workspace, int64_t workspace_bytes,
                        void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Weight-streaming GEMM for decode-sized batches — replaces the torch.matmul
+ * (cuBLAS) calls of a decode layer: core/layer/model_graph.py:145-147 (QKV
+ * projection; `bias` reproduces the separate bf16 add), :171 (o_proj), :183
+ * (gate_up), :185 (down_proj), on the [in, out]-contiguous weights of
+ * prepare_weights (:95-116).  SURVEY.md §8f N4.
+ *   out[m, n] = bf16( sum_k f32(x[m, k]) * f32(w[k, n]) )        (fp32 accumulate)
+ *   with bias: out = bf16( f32(bf16(sum)) + f32(bias[n]) )        (two roundings, like the reference)
+ * x [M, K] bf16, 1 <= M <= 64; w [K, N] bf16 row-major; K % 64 == 0, N % 64 == 0;
+ * strides in elements (x, w multiples of 8; out multiple of 4).  HBM-bound on w.
+ * ksplit: number of k-ranges (0 = b200_skinny_gemm_splits); variant: 0 = 128-column
+ * slices, 1 = 64, 2 = 256.  workspace (needed when ksplit > 1):
+ * b200_skinny_gemm_workspace_bytes(M, N, ksplit) bytes, 16-byte aligned, ZERO-FILLED
+ * ONCE by the caller; the kernel leaves its counters zeroed (graph-replay safe).
+ * Summation order is fixed (k ascending inside a range, ranges ascending): results
+ * are deterministic for a given (ksplit, variant).
+ * ------------------------------------------------------------------------ */
+int b200_skinny_gemm_splits(int M, int64_t K, int64_t N, int variant);
+int64_t b200_skinny_gemm_workspace_bytes(int M, int64_t N, int ksplit);
+int b200_skinny_gemm(const void* x, const void* w, const void* bias, void* out,
+                     void* workspace, int64_t workspace_bytes,
+                     int M, int64_t K, int64_t N,
+                     int64_t stride_x, int64_t stride_w, int64_t stride_out,
+                     int ksplit, int variant, void* stream);
 
 /* ------------------------------------------------------------------------ *
  * Paged decode attention — replaces the flash_attn_with_kvcache call at

@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "greedy_argmax", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
 ]
 
 
@@ -323,3 +323,46 @@ def greedy_argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
     check(lib.b200_greedy_argmax(logits.data_ptr(), _wdt(logits), rows, vocab, logits.stride(0) if rows > 1 else max(logits.stride(0), vocab),
                                  out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "b200_greedy_argmax")
     return out[:rows]
+
+
+# ------------------------------------------------------------------ decode-sized GEMM
+SKINNY_MAX_M = 64
+
+
+def skinny_gemm_ok(m: int, k: int, n: int) -> bool:
+    """Shapes ``b200_skinny_gemm`` accepts (1..64 rows, K % 64 == 0, N % 64 == 0)."""
+    return 1 <= m <= SKINNY_MAX_M and k > 0 and n > 0 and k % 64 == 0 and n % 64 == 0
+
+
+def skinny_gemm(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None,
+                bias: Optional[torch.Tensor] = None, ksplit: int = 0, variant: int = 0) -> torch.Tensor:
+    """out = x @ w (+ bias): x [M, K] bf16 with M <= 64, w [K, N] bf16 row-major (the ``[in, out]`` layout of
+    ``prepare_weights``, core/layer/model_graph.py:95-116).  Streams ``w`` once at HBM speed (split-K over
+    all SMs, deterministic merge); capturable.  The bias is added as a second bf16 rounding, like the
+    reference's separate ``qkv + bias`` (:147)."""
+    _req_cuda(x, w, out, bias)
+    assert x.dim() == 2 and w.dim() == 2 and x.shape[1] == w.shape[0], "skinny_gemm: x [M, K] @ w [K, N]"
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16, "skinny_gemm: bf16 only"
+    M, K = x.shape
+    N = w.shape[1]
+    assert skinny_gemm_ok(M, K, N), f"skinny_gemm: unsupported shape M={M} K={K} N={N}"
+    assert x.stride(1) == 1 and w.stride(1) == 1
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    assert out.dtype == torch.bfloat16 and out.shape == (M, N) and out.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.is_contiguous() and bias.numel() == N
+    if ksplit <= 0:
+        with torch.cuda.device(x.device):
+            ksplit = int(lib.b200_skinny_gemm_splits(M, K, N, int(variant)))
+    ksplit = max(1, min(int(ksplit), K // 64))
+    ws_ptr, ws_bytes = None, 0
+    if ksplit > 1:
+        ws = _workspace(x.device, int(lib.b200_skinny_gemm_workspace_bytes(M, N, ksplit)), "gemm")
+        ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
+    check(lib.b200_skinny_gemm(x.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None,
+                               out.data_ptr(), ws_ptr, ws_bytes, M, K, N,
+                               x.stride(0) if M > 1 else max(x.stride(0), K), w.stride(0),
+                               out.stride(0) if M > 1 else max(out.stride(0), N),
+                               int(ksplit), int(variant), _stream()), "b200_skinny_gemm")
+    return out

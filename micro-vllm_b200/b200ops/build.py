@@ -23,7 +23,7 @@ INCLUDE = os.path.join(os.path.dirname(ROOT), "include")
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(HERE, "libb200ops.so")
 
-SOURCES = ["elementwise.cu", "decode_attn.cu", "prefill_attn.cu", "allreduce_norm.cu", "sampling.cu"]
+SOURCES = ["elementwise.cu", "decode_attn.cu", "prefill_attn.cu", "allreduce_norm.cu", "sampling.cu", "skinny_gemm.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -71,6 +71,9 @@ class ModelGraphRunner:
         # writes the lengths, the block table or cached pages, so programmatic dependent launch
         # would be legal here; measured on B200 it does not pay (profiles/r01), so it stays off.
         self.use_pdl = 0
+        # Decode GEMMs at <= 64 rows stream the weights through b200_skinny_gemm (split-K over all SMs, SURVEY §8f
+        # N4) instead of cuBLAS; B200_SKINNY_GEMM=0 keeps torch.matmul everywhere.
+        self._skinny = os.environ.get("B200_SKINNY_GEMM", "0") == "1"
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
         self.rope = RoPE()
@@ -148,13 +151,19 @@ class ModelGraphRunner:
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
 
     # ------------------------------------------------------------------ per-layer pieces
+    def _mm(self, x, w, out, bias=None):
+        """out = x @ w (+ bias as a separate bf16 add, reference :145-147).  Decode-sized products take the
+        weight-streaming kernel when enabled; everything else is cuBLAS through torch.matmul."""
+        if self._skinny and b200ops.skinny_gemm_ok(x.shape[0], w.shape[0], w.shape[1]):
+            return b200ops.skinny_gemm(x, w, out=out, bias=bias)
+        torch.matmul(x, w, out=out)
+        if bias is not None:
+            out.add_(bias)
+        return out
+
     def _qkv_proj(self, block, bs):
         """QKV projection of ``self._normed[:bs]`` (the ln_1 norm was fused into the previous launch)."""
-        qkv = self._qkv[:bs]
-        torch.matmul(self._normed[:bs], block.attn._qkv_w, out=qkv)
-        if block.attn._qkv_b is not None:
-            qkv.add_(block.attn._qkv_b)
-        return qkv
+        return self._mm(self._normed[:bs], block.attn._qkv_w, self._qkv[:bs], block.attn._qkv_b)
 
     def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced=False):
         Hq, Hkv, D = self.num_heads, self.kv_num_heads, self.head_size
@@ -171,15 +180,12 @@ class ModelGraphRunner:
                                   cache_lens, block_table, softmax_scale=self.attention.scale,
                                   rotary_interleaved=False, out=attn, pdl=0 if balanced else self.use_pdl,
                                   balanced=balanced)
-        out = self._attn_out[:bs]
-        torch.matmul(self._attn[:bs], block.attn._o, out=out)
-        return out
+        return self._mm(self._attn[:bs], block.attn._o, self._attn_out[:bs])
 
     def _ffn(self, x_normed, block, bs, fast_mode=False):
-        torch.matmul(x_normed, block.mlp._gu, out=self._gate_up[:bs])
+        self._mm(x_normed, block.mlp._gu, self._gate_up[:bs])
         swiglu_gemm(self._gate_up[:bs], self._swiglu_out[:bs])
-        torch.matmul(self._swiglu_out[:bs], block.mlp._d, out=self._mlp_out[:bs])
-        return self._mlp_out[:bs]
+        return self._mm(self._swiglu_out[:bs], block.mlp._d, self._mlp_out[:bs])
 
     # ------------------------------------------------------------------ decode step
     def _reduce_add_norm(self, slot, x, residual, norm, y, res_out, ss_rounded):

@@ -58,6 +58,20 @@ def test_argument_errors_without_device():
     assert lib.b200_greedy_argmax(0x1000, 0, 4, 100000, 100000, 0x1000, 0x1000, 8, None) == _lib.E_RANGE
     assert lib.b200_greedy_argmax(0x1000, 0, 0, 100000, 100000, 0x1000, None, 0, None) == 0            # no rows: no-op
     assert lib.b200_greedy_argmax_workspace_bytes(32) == 512
+    gemm = lambda M, K, N, sx, sw, so, ws=None, wsb=0, ks=1: lib.b200_skinny_gemm(  # noqa: E731
+        0x1000, 0x1000, None, 0x1000, ws, wsb, M, K, N, sx, sw, so, ks, 0, None)
+    assert lib.b200_skinny_gemm(None, None, None, None, None, 0, 1, 64, 64, 64, 64, 64, 1, 0, None) == _lib.E_NULL
+    assert gemm(65, 64, 64, 64, 64, 64) == _lib.E_SHAPE                 # more than 64 rows
+    assert gemm(8, 100, 64, 104, 64, 64) == _lib.E_SHAPE                # K % 64
+    assert gemm(8, 64, 72, 64, 72, 72) == _lib.E_SHAPE                  # N % 64
+    assert gemm(8, 64, 64, 60, 64, 64) == _lib.E_ALIGN                  # stride_x < K
+    assert gemm(8, 64, 64, 64, 64, 66) == _lib.E_ALIGN                  # stride_out % 4
+    assert gemm(8, 256, 64, 256, 64, 64, None, 0, 2) == _lib.E_RANGE    # split-K without a workspace
+    assert gemm(0, 64, 64, 64, 64, 64) == 0                             # no rows: no-op
+    assert lib.b200_skinny_gemm_workspace_bytes(32, 4096, 1) == 16384
+    assert lib.b200_skinny_gemm_workspace_bytes(32, 4096, 9) == 16384 + 9 * 32 * 4096 * 4
+    assert lib.b200_skinny_gemm_splits(32, 100, 4096, 0) == -1
+    assert 1 <= lib.b200_skinny_gemm_splits(32, 14336, 4096, 0) <= 64
     a = _lib.DecodeArgs()
     for f in ("q", "k_cache", "v_cache", "cache_seqlens", "block_table", "out"):
         setattr(a, f, 0x1000)
