@@ -71,9 +71,12 @@ class ModelGraphRunner:
         # writes the lengths, the block table or cached pages, so programmatic dependent launch
         # would be legal here; measured on B200 it does not pay (profiles/r01), so it stays off.
         self.use_pdl = 0
-        # Decode GEMMs at <= 64 rows stream the weights through b200_skinny_gemm (split-K over all SMs, SURVEY §8f
-        # N4) instead of cuBLAS; B200_SKINNY_GEMM=0 keeps torch.matmul everywhere.
-        self._skinny = os.environ.get("B200_SKINNY_GEMM", "0") == "1"
+        # Decode GEMMs: B200_SKINNY_GEMM = "auto" (default) sends a product through the
+        # weight-streaming split-K kernel b200_skinny_gemm only where it was measured faster than cuBLAS on B200
+        # (profiles/r01/skinny_gemm_*.json): deep-K, narrow-N products at <= 32 rows — down_proj, where cuBLAS
+        # launches N/64 CTAs without split-K and reaches 0.5 of the HBM roofline (36.7 us vs 25.7 us for
+        # [32, 14336] x [14336, 4096]); "1" forces it for every shape it supports, "0" keeps torch.matmul everywhere.
+        self._skinny = os.environ.get("B200_SKINNY_GEMM", "auto")
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
         self.rope = RoPE()
@@ -154,8 +157,12 @@ class ModelGraphRunner:
     def _mm(self, x, w, out, bias=None):
         """out = x @ w (+ bias as a separate bf16 add, reference :145-147).  Decode-sized products take the
         weight-streaming kernel when enabled; everything else is cuBLAS through torch.matmul."""
-        if self._skinny and b200ops.skinny_gemm_ok(x.shape[0], w.shape[0], w.shape[1]):
-            return b200ops.skinny_gemm(x, w, out=out, bias=bias)
+        m, (k, n) = x.shape[0], w.shape
+        if self._skinny != "0" and b200ops.skinny_gemm_ok(m, k, n):
+            if self._skinny == "1":
+                return b200ops.skinny_gemm(x, w, out=out, bias=bias)
+            if m <= 32 and k >= 2 * n:
+                return b200ops.skinny_gemm(x, w, out=out, bias=bias, variant=1)      # 64-column slices
         torch.matmul(x, w, out=out)
         if bias is not None:
             out.add_(bias)

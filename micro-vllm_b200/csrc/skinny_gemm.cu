@@ -25,7 +25,12 @@ namespace b200 {
 
 constexpr int SG_THREADS = 256;          // 8 warps = 4 column groups (BN / 4 columns each) x 2 halves of a stage's rows
 constexpr int SG_KC = 64;                // W rows per stage; warps 0-3 take rows 0-31, warps 4-7 rows 32-63
-constexpr int SG_STAGES = 4;
+// ring depth: as many stages as fit in ~110 KB (two CTAs per SM), between 3 and 8 — the bytes in flight per SM
+// ((stages - 1) x stage x 2 CTAs = 130-170 KB) are what keeps HBM busy at its loaded latency
+__host__ __device__ constexpr int sg_stage_bytes(int mt, int bn) { return SG_KC * bn * 2 + 16 * mt * SG_KC * 2; }
+__host__ __device__ constexpr int sg_stages(int mt, int bn) {
+    return 110 * 1024 / sg_stage_bytes(mt, bn) > 8 ? 8 : (110 * 1024 / sg_stage_bytes(mt, bn) < 3 ? 3 : 110 * 1024 / sg_stage_bytes(mt, bn));
+}
 constexpr int SG_COUNTERS = 4096;        // arrival counters at the head of the workspace (one per column slice)
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
@@ -58,12 +63,13 @@ struct SkinnyParams {
 
 // MT = number of 16-row tiles of x (M <= 16 * MT); BN = columns per CTA (64 / 128 / 256).
 template <int MT, int BN>
-__global__ void __launch_bounds__(SG_THREADS)
+__global__ void __launch_bounds__(SG_THREADS, (MT == 4 && BN == 256) ? 1 : 2)
 skinny_gemm_kernel(const SkinnyParams p) {
     constexpr int WCH = BN / 8;                         // 16-byte chunks per W tile row
     constexpr int W_STAGE = SG_KC * BN * 2;             // bytes
     constexpr int X_STAGE = 16 * MT * SG_KC * 2;
     constexpr int NT2 = BN / 64;                        // ldmatrix.x4.trans per k16 per warp (2 n8 tiles each)
+    constexpr int SG_STAGES = sg_stages(MT, BN);
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t sW = smem_u32(smem);
     const uint32_t sX = sW + SG_STAGES * W_STAGE;
@@ -80,23 +86,45 @@ skinny_gemm_kernel(const SkinnyParams p) {
         if (row >= p.M) *reinterpret_cast<uint4*>(smem + SG_STAGES * W_STAGE + (size_t)i * 16) = make_uint4(0, 0, 0, 0);
     }
 
-    auto load_stage = [&](int it, int slot) {
-        const int64_t k0 = (int64_t)(u0 + it) * SG_KC;
-        const __nv_bfloat16* wsrc = p.w + k0 * p.ldw + n0;
-        const uint32_t wdst = sW + slot * W_STAGE;
+    // Per-thread copy plan, hoisted out of the loop (the ncu source view of the first version showed ~150 issued
+    // instructions per warp and stage, two thirds of them address arithmetic: the kernel was issue bound, not
+    // memory bound).  Thread t copies chunk c = t % WCH of rows t / WCH + i * (256 / WCH): the swizzle term
+    // (row & 7) is the same for every i, so destinations are dst0 + i * 4096 and sources advance by a constant.
+    constexpr int NW = SG_KC * WCH / SG_THREADS;        // W chunks per thread and stage (2 / 4 / 8)
+    constexpr int NX = (MT + 1) / 2;                    // x chunks per thread and stage
+    const int wrow0 = tid / WCH, wc = tid % WCH;
+    uint32_t w_dst0 = sW + wrow0 * (BN * 2) + ((wc ^ (wrow0 & 7)) << 4);
+    asm volatile("" : "+r"(w_dst0));
+    const int64_t w_rstep = (int64_t)(SG_THREADS / WCH) * p.ldw;             // elements between a thread's rows
+    const __nv_bfloat16* w_src[NW];                     // one live pointer per copy: 2 integer adds per stage each
 #pragma unroll
-        for (int i = 0; i < SG_KC * WCH / SG_THREADS; ++i) {
-            const int idx = tid + i * SG_THREADS;
-            const int row = idx / WCH, c = idx % WCH;
-            cp_async16(wdst + row * (BN * 2) + ((c ^ (row & 7)) << 4), wsrc + (int64_t)row * p.ldw + c * 8);
-        }
-        const uint32_t xdst = sX + slot * X_STAGE;
+    for (int i = 0; i < NW; ++i) {
+        w_src[i] = p.w + ((int64_t)u0 * SG_KC + wrow0) * p.ldw + n0 + wc * 8 + i * w_rstep;
+        asm volatile("" : "+l"(w_src[i]));              // opaque: keep it in a register instead of recomputing from tid
+    }
+    int64_t w_kstep = (int64_t)SG_KC * p.ldw * 2;       // bytes
+    asm volatile("" : "+l"(w_kstep));
+    const int xrow0 = tid >> 3, xc = tid & 7;
+    uint32_t x_dst0 = sX + xrow0 * 128 + ((xc ^ (xrow0 & 7)) << 4);
+    const __nv_bfloat16* x_src = p.x + (int64_t)xrow0 * p.ldx + (int64_t)u0 * SG_KC + xc * 8;
+    asm volatile("" : "+r"(x_dst0), "+l"(x_src));
+    const int64_t x_rstep = 32 * p.ldx;
+    bool x_ok[NX];
 #pragma unroll
-        for (int i = 0; i < (MT + 1) / 2; ++i) {
-            const int idx = tid + i * SG_THREADS;
-            const int row = idx >> 3, c = idx & 7;
-            if (row < p.M) cp_async16(xdst + row * 128 + ((c ^ (row & 7)) << 4), p.x + (int64_t)row * p.ldx + k0 + c * 8);
+    for (int i = 0; i < NX; ++i) x_ok[i] = (xrow0 + 32 * i < p.M) && (xrow0 + 32 * i < 16 * MT);
+
+    auto load_stage = [&](int slot) {                   // loads the NEXT stage of this CTA's k-range into `slot`
+        const uint32_t wdst = slot * W_STAGE + w_dst0;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            cp_async16(wdst + i * 4096, w_src[i]);
+            w_src[i] = reinterpret_cast<const __nv_bfloat16*>(reinterpret_cast<const char*>(w_src[i]) + w_kstep);
         }
+        const uint32_t xdst = slot * X_STAGE + x_dst0;
+#pragma unroll
+        for (int i = 0; i < NX; ++i)
+            if (x_ok[i]) cp_async16(xdst + i * 4096, x_src + i * x_rstep);
+        x_src += SG_KC;
     };
 
     float acc[MT][2 * NT2][4];
@@ -109,36 +137,44 @@ skinny_gemm_kernel(const SkinnyParams p) {
 
 #pragma unroll
     for (int s = 0; s < SG_STAGES - 1; ++s) {
-        if (s < n_it) load_stage(s, s);
+        if (s < n_it) load_stage(s);
         cp_async_commit();
     }
     const int lrow = lane & 7, lmat = lane >> 3;
     const int cgrp = warp & 3, khalf = warp >> 2;       // column group, half of the stage's 64 rows
+    // ldmatrix offsets inside a stage: x rows m*16 + ... differ by m * 2048 bytes (same swizzle term)
+    uint32_t a_off[2], b_off[2][NT2];
+#pragma unroll
+    for (int k2 = 0; k2 < 2; ++k2) {
+        const int kk = khalf * 2 + k2;
+        const int row = (lmat & 1) * 8 + lrow;
+        const int ca = kk * 2 + (lmat >> 1);
+        a_off[k2] = row * 128 + ((ca ^ (row & 7)) << 4);
+        const int krow = kk * 16 + (lmat & 1) * 8 + lrow;
+#pragma unroll
+        for (int t = 0; t < NT2; ++t) {
+            const int c = cgrp * (BN / 32) + t * 2 + (lmat >> 1);
+            b_off[k2][t] = sW + krow * (BN * 2) + ((c ^ (krow & 7)) << 4);
+            asm volatile("" : "+r"(b_off[k2][t]));
+        }
+        a_off[k2] += sX;
+        asm volatile("" : "+r"(a_off[k2]));
+    }
+    int slot = 0, lslot = SG_STAGES - 1;
     for (int it = 0; it < n_it; ++it) {
         cp_async_wait<SG_STAGES - 2>();
         __syncthreads();                                // stage `it` visible to all; slot of stage it-1 is free
-        if (it + SG_STAGES - 1 < n_it) load_stage(it + SG_STAGES - 1, (it + SG_STAGES - 1) % SG_STAGES);
+        if (it + SG_STAGES - 1 < n_it) load_stage(lslot);
         cp_async_commit();
-        const int slot = it % SG_STAGES;
-        const uint32_t wbase = sW + slot * W_STAGE, xbase = sX + slot * X_STAGE;
-        // every fragment of this warp's two k16 steps is requested before the first mma: one exposed
-        // shared-memory latency per stage instead of one per ldmatrix
+        const uint32_t wbase = slot * W_STAGE, xbase = slot * X_STAGE;
+        // every fragment of this warp's two k16 steps is requested before the first mma
         uint32_t a[2][MT][4], b[2][NT2][4];
 #pragma unroll
         for (int k2 = 0; k2 < 2; ++k2) {
-            const int kk = khalf * 2 + k2;
 #pragma unroll
-            for (int m = 0; m < MT; ++m) {
-                const int row = m * 16 + (lmat & 1) * 8 + lrow;
-                const int c = kk * 2 + (lmat >> 1);
-                ldsm_x4(xbase + row * 128 + ((c ^ (row & 7)) << 4), a[k2][m]);
-            }
+            for (int m = 0; m < MT; ++m) ldsm_x4(xbase + a_off[k2] + m * 2048, a[k2][m]);
 #pragma unroll
-            for (int t = 0; t < NT2; ++t) {
-                const int krow = kk * 16 + (lmat & 1) * 8 + lrow;
-                const int c = cgrp * (BN / 32) + t * 2 + (lmat >> 1);
-                ldsm_x4_trans(wbase + krow * (BN * 2) + ((c ^ (krow & 7)) << 4), b[k2][t]);
-            }
+            for (int t = 0; t < NT2; ++t) ldsm_x4_trans(wbase + b_off[k2][t], b[k2][t]);
         }
 #pragma unroll
         for (int k2 = 0; k2 < 2; ++k2)
@@ -149,6 +185,8 @@ skinny_gemm_kernel(const SkinnyParams p) {
                     mma_bf16(acc[m][2 * t], a[k2][m], b[k2][t][0], b[k2][t][1]);
                     mma_bf16(acc[m][2 * t + 1], a[k2][m], b[k2][t][2], b[k2][t][3]);
                 }
+        slot = (slot + 1 == SG_STAGES) ? 0 : slot + 1;
+        lslot = (lslot + 1 == SG_STAGES) ? 0 : lslot + 1;
     }
     cp_async_wait<0>();
     __syncthreads();                                    // pipeline buffers are free: reuse them for the k-half merge
@@ -212,24 +250,30 @@ skinny_gemm_kernel(const SkinnyParams p) {
                 const int64_t col = n0 + wcol + n * 8 + q * 2;
                 *reinterpret_cast<float2*>(part + (int64_t)row * p.N + col) = make_float2(acc[m][n][2 * h], acc[m][n][2 * h + 1]);
             }
-    __threadfence();
-    __syncthreads();
+    __syncthreads();                                    // every partial store of this CTA happens-before thread 0's release
     __shared__ unsigned int s_last;
     if (tid == 0) {
-        const unsigned int prev = atomicAdd(p.counters + blockIdx.x, 1u);
+        unsigned int prev;                              // one acq_rel atomic per CTA (cumulative over the barrier)
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(p.counters + blockIdx.x) : "memory");
         s_last = (prev == (unsigned int)p.KS - 1) ? 1u : 0u;
     }
     __syncthreads();
     if (!s_last) return;
-    __threadfence();
     constexpr int V4 = BN / 4;                          // float4 per row of the slice
     for (int i = tid; i < p.M * V4; i += SG_THREADS) {
         const int row = i / V4, c4 = i % V4;
         const int64_t col = n0 + c4 * 4;
         float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int z = 0; z < p.KS; ++z) {
-            const float4 v = __ldcg(reinterpret_cast<const float4*>(p.partial + ((int64_t)z * p.M + row) * p.N + col));
-            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        const float* src = p.partial + (int64_t)row * p.N + col;
+        const int64_t zs = (int64_t)p.M * p.N;
+        for (int z0 = 0; z0 < p.KS; z0 += 8) {          // 8 independent L2 loads in flight, summed in k-range order
+            float4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (z0 + j < p.KS) v[j] = __ldcg(reinterpret_cast<const float4*>(src + (z0 + j) * zs));
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (z0 + j < p.KS) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
         }
         uint32_t lo = pack_bf16(s.x, s.y), hi = pack_bf16(s.z, s.w);
         if (p.bias) {
@@ -244,7 +288,7 @@ skinny_gemm_kernel(const SkinnyParams p) {
 
 template <int MT, int BN>
 static int launch_skinny(const SkinnyParams& p, cudaStream_t st) {
-    constexpr int smem = SG_STAGES * (SG_KC * BN * 2 + 16 * MT * SG_KC * 2);
+    constexpr int smem = sg_stages(MT, BN) * sg_stage_bytes(MT, BN);
     // not a stream operation (legal during capture); per device, so it is not cached in a static
     cudaError_t e = cudaFuncSetAttribute(skinny_gemm_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("skinny_gemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
@@ -259,16 +303,16 @@ static int skinny_bn(int variant, int64_t N) {
     return bn;
 }
 
-// split count from launch constants only: fill `ctas_per_sm` resident CTAs on every SM, at least 4 stages per range
+// split count from launch constants only: fill `ctas_per_sm` resident CTAs on every SM, at least 8 stages per range
 static int skinny_auto_ks(int M, int64_t K, int64_t N, int bn, int n_sm) {
     const int mt = M <= 16 ? 1 : (M <= 32 ? 2 : 4);
-    const int smem = SG_STAGES * (SG_KC * bn * 2 + 16 * mt * SG_KC * 2);
+    const int smem = sg_stages(mt, bn) * sg_stage_bytes(mt, bn);
     int per_sm = (int)(220 * 1024 / smem);
     if (per_sm > 4) per_sm = 4;
     if (per_sm < 1) per_sm = 1;
     const int64_t slices = N / bn, units = K / SG_KC;
     int64_t ks = ((int64_t)n_sm * per_sm) / slices;
-    if (ks > units / 4) ks = units / 4;
+    if (ks > units / 8) ks = units / 8;
     if (ks < 1) ks = 1;
     if (ks > 64) ks = 64;
     return (int)ks;
