@@ -4,19 +4,22 @@
 //   (:95-116) transposed to [in, out] contiguous — SURVEY.md §8f N4 (the GEMMs either side of the path).
 //
 // At M <= 64 these products are HBM-bound on the weight matrix (K*N*2 bytes read once; 2*M flops per
-// weight byte pair): the job is to stream W at the HBM roofline, not to feed the tensor cores.  cuBLAS
-// picks output-tile grids without split-K for these shapes, so a [32, 14336] x [14336, 4096] product runs
-// on 64 CTAs at ~0.5 of the roofline (profiles/r01/layer_*.json).  Here:
-//   * grid = (N / BN column slices, KS k-ranges) sized to a whole number of resident CTAs per SM;
-//   * every CTA streams its [k-range, BN] panel of W through a 4-stage cp.async ring (64 rows x BN columns
-//     per stage, 128-bit copies, XOR-swizzled for conflict-free ldmatrix) together with the matching
-//     [M, 64] slab of x (L2 resident: x is tiny and shared by all column slices);
+// weight): the job is to stream W at the HBM roofline, not to feed the tensor cores.  cuBLAS picks
+// output-tile grids without split-K for deep-K narrow-N shapes, so a [32, 14336] x [14336, 4096] product runs
+// on 64 CTAs at 0.5 of the roofline (profiles/r01/skinny_gemm_*.json).  Here:
+//   * grid = (N / BN column slices, KS k-ranges) sized to the resident CTAs of all SMs;
+//   * 256 threads = 4 column groups x 2 halves of a 64-row stage; every CTA streams its [k-range, BN] panel of
+//     W through a 3-8 stage cp.async ring (~100 KB, two CTAs per SM; 128-bit copies, XOR-swizzled for
+//     conflict-free ldmatrix) together with the matching [M, 64] slab of x (L2 resident: x is tiny and shared
+//     by all column slices).  The per-thread copy plan (pointers, swizzled offsets) lives in registers: the
+//     first version recomputed it from threadIdx every stage and was instruction-issue bound (ncu);
 //   * mma.sync m16n8k16 bf16 -> fp32 with x as the row operand (ldmatrix) and W as the column operand
-//     (ldmatrix.trans straight from the [k][n] tile) — tensor cores only because 2*M flops per byte would
-//     saturate the FMA pipes, not because the kernel is compute bound;
-//   * split-K partials go to an fp32 workspace and the LAST CTA to arrive on a column slice (one atomic per
-//     CTA) sums them in k-range order — deterministic, one launch, CUDA-graph replay safe (the counter is
-//     reset by that CTA);
+//     (ldmatrix.trans straight from the [k][n] tile); all fragments of a stage are requested before the first
+//     mma.  The legacy tensor path sustains one HMMA per 8 clk per sub-partition on B200 (tools/micro), the
+//     roofline needs one per 22 (M = 32) / 11 (M = 64);
+//   * the two k-halves of a CTA merge through shared memory; split-K partials go to an fp32 workspace and the
+//     LAST CTA to arrive on a column slice (one acq_rel atomic per CTA) sums them in k-range order —
+//     deterministic, one launch, CUDA-graph replay safe (the counter is reset by that CTA);
 //   * epilogue rounds once to bf16; a bias is added the way the reference does it (bf16 matmul result, then
 //     a bf16 add: two roundings).
 #include "common.cuh"
