@@ -347,6 +347,20 @@ def run_b200_arm(args):
         dt, nb = arm.time(reps), arm.nbytes
         cpu = {"value": round(nb / dt / 1e9, 4), "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{rows} of {B} batch rows, 1 layer call, mean of {reps} calls (oracle port, torch eager)"}
+    # auxiliary (N = 1 only, outside the timed region of the headline metric): decode tokens/s of the whole
+    # Llama-3-8B-shaped layer stack through the reference-shaped runner, i.e. the second half of BASELINE.json's metric
+    step = None
+    if world == 1 and not args.no_decode_step:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            from bench_decode_step import run as run_step
+            r = run_step("llama3-8b", layers=L, batch=B, ctx=per_seq * page, steps=20, warmup=3)
+            step = {"tokens_per_s": r["tokens_per_s_run"], "ms_per_step": r["ms_per_step_run"], "tp": 1,
+                    "workload": f"llama3-8b-shape {L}-layer decode step through ModelGraphRunner (CUDA graph), batch {B}, "
+                                f"ctx {per_seq * page}, random-init weights, lm_head included",
+                    "skinny_gemm": os.environ.get("B200_SKINNY_GEMM", "auto")}
+        except Exception as e:  # noqa: BLE001 - auxiliary figure must never take the headline line down
+            step = {"error": f"{type(e).__name__}: {e}"[:300]}
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "decode_traffic.json")
     if os.path.exists(tpath):
@@ -371,6 +385,7 @@ def run_b200_arm(args):
         "gpu_launches": args.steps * L,
         "clocks": clk.summary(),
         "tokens_per_s_attention_only": round(world * B / (ms_step * 1e-3), 1),
+        "decode_step": step,
     }
     print(json.dumps(line), flush=True)
 
@@ -384,6 +399,7 @@ def main():
     ap.add_argument("--splits", type=int, default=0, help="override the split-KV count (0 = heuristic)")
     ap.add_argument("--variant", type=int, default=0, help="decode kernel tuning variant")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-decode-step", action="store_true", help="skip the auxiliary whole-model decode tokens/s figure")
     ap.add_argument("--pdl", type=int, default=0, help="programmatic dependent launch: 0 off, 1 early trigger, 2 late trigger")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
