@@ -143,3 +143,22 @@ def test_split_heuristic_is_launch_constant():
     assert decode_num_splits(8, 8, 512 * 256) == 4           # 256 CTAs, one wave
     assert decode_num_splits(1, 8, 16 * 256) == 16
     assert decode_num_splits(64, 8, 32 * 256) >= 1
+
+
+def test_sampler_and_new_ops_refuse_cpu_and_unsupported_modes():
+    import torch
+    import b200ops
+    from core.layer.sampler import Sampler
+    logits = torch.zeros(2, 64, dtype=torch.bfloat16)
+    ones = torch.ones(2)
+    with pytest.raises(NotImplementedError):                # stochastic sampling is outside the hot-path scope
+        Sampler()(logits, ones, ones, 50)
+    with pytest.raises(AssertionError):                     # greedy: CUDA tensors only, no fallback
+        Sampler()(logits, ones, ones, 1)
+    with pytest.raises(AssertionError):
+        b200ops.greedy_argmax(logits)
+    with pytest.raises(AssertionError):
+        b200ops.skinny_gemm(torch.zeros(4, 64, dtype=torch.bfloat16), torch.zeros(64, 64, dtype=torch.bfloat16))
+    assert b200ops.skinny_gemm_ok(32, 14336, 4096) and b200ops.skinny_gemm_ok(1, 64, 64)
+    assert not b200ops.skinny_gemm_ok(65, 4096, 4096) and not b200ops.skinny_gemm_ok(0, 64, 64)
+    assert not b200ops.skinny_gemm_ok(8, 4096 + 32, 4096) and not b200ops.skinny_gemm_ok(8, 4096, 4096 + 8)
