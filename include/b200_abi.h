@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 11
+#define B200_ABI_VERSION 12
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -334,6 +334,9 @@ typedef struct b200_ar_args {
     void*   ystage_peers[B200_AR_MAX_WORLD];  /* LL form: rank r's staging for pushed normalised rows */
     void*   trace;            /* optional uint64 [min(rows, MAX_CTAS)][4]: %globaltimer (ns) at kernel start, barrier
                                  passed, rows reduced, end of every CTA (tools/bench_allreduce.py); NULL = off        */
+    const void* x_mc;         /* NVLS form: multicast address of the x slot (same offset as x_peers[rank])            */
+    void*       y_mc;         /* NVLS form: multicast address of the y buffer (same offset as y)                      */
+    void*       flags_mc;     /* NVLS form: multicast address of the flag region (same offset as flag_peers[rank])    */
 } b200_ar_args;
 
 /* Row-sharded ("two-shot") form for world > 1, rows <= B200_AR_MAX_CTAS: rank r OWNS rows
@@ -357,6 +360,17 @@ typedef struct b200_ar_args {
  * rows * n * 4 bytes.  epoch words [B200_AR_MAX_CTAS + 1] (call counter) and [+2] (arrival counter) are
  * used: `epoch` must hold B200_AR_MAX_CTAS + 4 words. */
 #define B200_AR_MODE_LL 2
+
+/* NVLS form (in-switch reduction; the form SURVEY.md §8f N1 names): every rank's slab is bound to ONE multicast
+ * object (cuMulticastCreate / cuMulticastBindMem; `x_mc`, `y_mc`, `flags_mc` are addresses inside its mapping).
+ * Row ownership and the row-sharded residual contract are those of ROW_SHARDED.  The owner of a row reads the SUM
+ * of the row over all ranks with multimem.ld_reduce (fp32 accumulation inside the NVSwitch, one bf16 rounding),
+ * adds its residual row, normalises, and multimem.st's y into EVERY rank's y buffer; the two flag hops are
+ * multimem.red on monotonic counters (u32 words B200_AR_MAX_CTAS * (B200_AR_MAX_WORLD + 1) and + 32 of every
+ * rank's flag region; local targets in epoch words [B200_AR_MAX_CTAS + 4 .. + 6], so `epoch` must hold
+ * B200_AR_MAX_CTAS + 8 words).  grid = ceil(rows / world) CTAs per rank.  When the call returns on any rank every
+ * owner has finished reading x: the x slot may be rewritten immediately (no slot alternation). */
+#define B200_AR_MODE_NVLS 4
 
 int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
 

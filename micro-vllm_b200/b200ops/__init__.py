@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "decode_num_splits", "decode_use_balanced", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "decode_num_splits", "decode_use_balanced", "decode_algorithmic_bytes", "reserve_graph_workspace", "B200Error", "LIB_PATH",
 ]
 
 
@@ -128,6 +128,17 @@ def decode_num_splits(batch: int, kv_heads: int, capacity_tokens: int, n_sm: int
     return int(max(1, min(want, cap, 128)))
 
 
+def decode_algorithmic_bytes(seqlens_after, Hq: int, Hkv: int, D: int, block_size: int = 256, elt: int = 2) -> int:
+    """Algorithmic HBM bytes of one decode attention call: K and V read once per KV
+    head over the ``len_b + 1`` keys of every row, the new K / V rows written, q read and out written,
+    the sequence lengths and the USED block-table entries read.  Split-KV scratch is not counted."""
+    B = len(seqlens_after)
+    total = 0
+    for n in seqlens_after:
+        total += int(n) * 2 * Hkv * D * elt + 4 * (-(-int(n) // block_size))
+    return total + B * 2 * Hkv * D * elt + 2 * B * Hq * D * elt + 4 * B
+
+
 _BALANCED_ENV = None
 
 
@@ -151,8 +162,24 @@ _RETIRED: list = []
 def _workspace(device: torch.device, nbytes: int, tag: str) -> torch.Tensor:
     """Per (device, stream, operator) scratch.  Zero-filled once: the decode arrival
     counters must start at 0 and the kernel resets them itself.  Outgrown buffers are
-    kept alive because captured CUDA graphs may still hold their addresses."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+    kept alive because captured CUDA graphs may still hold their addresses.
+
+    Launches recorded into a CUDA graph use ONE scratch per (device, operator) that every
+    graph shares.  It is allocated and zeroed by the eager calls that precede a capture (the
+    warm-up every capture needs anyway), never inside a capture: an allocation made while
+    capturing lands in that graph's private pool and its zero fill becomes a memset node of
+    that graph alone, so other graphs would find whatever the pool held."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    gkey = (idx, "graph", tag)
+    if torch.cuda.is_current_stream_capturing():
+        ws = _WORKSPACES.get(gkey)
+        if ws is None or ws.numel() < nbytes:
+            raise RuntimeError(
+                f"b200ops: the '{tag}' scratch for captured launches ({nbytes} bytes) does not exist yet; run the "
+                "same call once eagerly (warm-up) or call b200ops.reserve_graph_workspace() before torch.cuda.graph")
+        return ws
+    reserve_graph_workspace(device, nbytes, tag)
+    key = (idx, torch.cuda.current_stream(device).cuda_stream, tag)
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() < nbytes:
         if ws is not None:
@@ -160,6 +187,20 @@ def _workspace(device: torch.device, nbytes: int, tag: str) -> torch.Tensor:
         ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _WORKSPACES[key] = ws
     return ws
+
+
+def reserve_graph_workspace(device: torch.device, nbytes: int, tag: str) -> None:
+    """Make sure the scratch that CAPTURED launches of operator ``tag`` use holds ``nbytes``
+    zeroed bytes.  Must run outside a capture; every eager launch does it implicitly."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    gkey = (idx, "graph", tag)
+    ws = _WORKSPACES.get(gkey)
+    if ws is None or ws.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("b200ops.reserve_graph_workspace: cannot allocate during a CUDA graph capture")
+        if ws is not None:
+            _RETIRED.append(ws)
+        _WORKSPACES[gkey] = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=torch.device("cuda", idx))
 
 
 def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 
 class DecodeArgs(C.Structure):
@@ -68,6 +68,9 @@ class PrefillArgs(C.Structure):
 AR_MAX_WORLD, AR_MAX_CTAS, IPC_HANDLE_BYTES = 8, 1024, 64
 AR_MODE_ROW_SHARDED = 1
 AR_MODE_LL = 2
+AR_MODE_NVLS = 4
+AR_NVLS_READY_WORD = AR_MAX_CTAS * (AR_MAX_WORLD + 1)
+AR_NVLS_DONE_WORD = AR_NVLS_READY_WORD + 32
 
 
 class ArArgs(C.Structure):
@@ -81,6 +84,7 @@ class ArArgs(C.Structure):
         ("ss_rounded", _i32), ("timeout_ms", _i32), ("mode", _i32),
         ("y_peers", _vp * AR_MAX_WORLD),
         ("xstage_peers", _vp * AR_MAX_WORLD), ("ystage_peers", _vp * AR_MAX_WORLD), ("trace", _vp),
+        ("x_mc", _vp), ("y_mc", _vp), ("flags_mc", _vp),
     ]
 
 

@@ -4,22 +4,32 @@ kernel (``b200_allreduce_residual_rmsnorm``, include/b200_abi.h).
 Replaces, on the decode path, the NCCL ``all_reduce`` of core/parallel_config.py:65-69 and the
 elementwise kernels that follow it at core/layer/model_graph.py:210-216 and :219/:143.
 
-One process per GPU.  Every rank cudaMalloc's ONE slab (IPC-exportable, outside torch's caching
-allocator), laid out as
+One process per GPU.  Every rank owns ONE symmetric slab, laid out as
 
-    [ flags u32[1024][8] + u32[1024] | epoch u32[1028] (local only) | pad | slot 0 | slot 1 | y |
-      x staging (LL) | y staging (LL) ]
+    [ flags u32[1024][8] + u32[1024] + NVLS counters | epoch u32[1032] (local only) | pad | slot 0 |
+      slot 1 | y | x staging (LL) | y staging (LL) ]
 
-exports it with cudaIpcGetMemHandle, exchanges the 64-byte handles through torch.distributed
-(plumbing only) and maps every peer's slab.  The two data slots are the GEMM output buffers the
-kernel reads on every rank; consecutive calls must alternate slots (the barrier of call k+1 proves
-that all peers finished reading the slot of call k), which :meth:`allreduce_residual_rmsnorm`
-enforces on the host at call / capture time.  ``y`` is the peer-visible output buffer of the
-row-sharded form, in which the owner of a row pushes the normalised row to every rank.
+and maps every peer's slab.  Two plumbing back ends provide the slab (``B200_COMM_BACKEND`` =
+``auto`` | ``symm`` | ``ipc``):
+
+  * ``symm`` — ``torch.distributed._symmetric_memory`` (cuMemCreate + fabric / fd handles exchanged
+    through the process group's store, plumbing only): peer pointers AND, when the node has an
+    NVSwitch with multicast support, ONE multicast address range bound to all ranks' slabs.  The
+    multicast range is what the NVLS form of the kernel (``multimem.ld_reduce`` / ``multimem.st`` /
+    ``multimem.red``: the reduction happens inside the switch) runs on.
+  * ``ipc`` — ``cudaMalloc`` + ``cudaIpcGetMemHandle`` exchanged through torch.distributed; peer
+    pointers only (one-shot / row-sharded / LL forms).
+
+The two data slots are the GEMM output buffers the kernel reads on every rank.  In the one-shot form
+consecutive calls must alternate slots (the barrier of call k+1 proves that all peers finished reading
+the slot of call k), which :meth:`allreduce_residual_rmsnorm` enforces on the host at call / capture
+time; the other forms end with a barrier of their own.  ``y`` is the peer-visible output buffer of the
+row-sharded and NVLS forms, in which the owner of a row pushes the normalised row to every rank.
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -27,9 +37,14 @@ import torch
 from . import _lib
 from ._lib import ArArgs, check, lib
 
-_FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4        # ready flags [1024][8] + done flags [1024]
-_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 4) * 4 + 255) // 256 * 256     # per-CTA epochs, error word, LL call + arrival counters
+# ready flags [1024][8] + done flags [1024] + the two NVLS counters (128 bytes apart)
+_FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4 + 256
+# per-CTA epochs, error word, LL call + arrival counters, NVLS targets + arrival counter
+_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 8) * 4 + 255) // 256 * 256
 _HEADER = _FLAG_BYTES + _EPOCH_BYTES
+_ERR_OFF = _FLAG_BYTES + _lib.AR_MAX_CTAS * 4
+
+MODES = ("oneshot", "sharded", "ll", "nvls")
 
 
 class _DevMem:
@@ -88,7 +103,8 @@ def _fill_common(a: ArArgs, x, residual, weight, y, res_out, eps, ss_rounded):
 class PeerComm:
     """Two symmetric bf16 slots of ``slot_bytes`` each on every rank of ``group`` + flag arrays."""
 
-    def __init__(self, slot_bytes: int, group=None, device: Optional[torch.device] = None, timeout_ms: int = 2000):
+    def __init__(self, slot_bytes: int, group=None, device: Optional[torch.device] = None, timeout_ms: int = 2000,
+                 backend: Optional[str] = None):
         import torch.distributed as dist
         assert dist.is_initialized(), "PeerComm needs torch.distributed (one process per GPU)"
         self.group = group if group is not None else dist.group.WORLD
@@ -103,16 +119,80 @@ class PeerComm:
         self._xstage_bytes = 2 * self.slot_bytes + self.world * 16384 * 4
         self._ystage_off = self._xstage_off + self._xstage_bytes
         total = self._ystage_off + 2 * self.slot_bytes
+        self._total = total
+        self._imported: List[int] = []
+        self._symm = None
+        self._mc_base = 0
+        want = (backend or os.environ.get("B200_COMM_BACKEND", "auto")).lower()
+        assert want in ("auto", "symm", "ipc"), f"B200_COMM_BACKEND={want} (auto | symm | ipc)"
+        self.backend = None
+        self.backend_note = ""
+        if want in ("auto", "symm"):
+            ok, why = self._try_symm(total)
+            flags = [None] * self.world
+            dist.all_gather_object(flags, bool(ok), group=self.group)
+            if all(flags):
+                self.backend = "symm"
+            else:
+                self._drop_symm()
+                self.backend_note = why or "a peer could not set up symmetric memory"
+                if want == "symm":
+                    raise RuntimeError(f"PeerComm: torch symmetric memory unavailable: {self.backend_note}")
+        if self.backend is None:
+            self._init_ipc(total)
+            self.backend = "ipc"
+        # every rank must agree on whether the multicast range exists
+        mc = [None] * self.world
+        dist.all_gather_object(mc, bool(self._mc_base), group=self.group)
+        if not all(mc):
+            self._mc_base = 0
+        self.has_multicast = bool(self._mc_base)
+        assert self._bytes.data_ptr() == self._base and self._bytes.numel() >= total
+        self._last_slot, self._last_mode = -1, None
+        self._err_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._err_event: Optional[torch.cuda.Event] = None
+        self._err_calls = 0
+        dist.barrier(group=self.group)          # nobody launches before every rank has mapped every slab
+
+    # ------------------------------------------------------------------ plumbing back ends
+    def _try_symm(self, total: int):
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            with torch.cuda.device(self.device):
+                t = symm_mem.empty(total, dtype=torch.uint8, device=self.device)
+                hdl = symm_mem.rendezvous(t, self.group)
+                t.zero_()
+                torch.cuda.synchronize(self.device)
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            off = int(t.data_ptr()) - ptrs[self.rank]
+            if len(ptrs) != self.world or off < 0:
+                return False, "unexpected symmetric memory layout"
+            self._symm = (t, hdl)
+            self._bytes = t
+            self._base = int(t.data_ptr())
+            self._peer_base = [p + off for p in ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            self._mc_base = mc + off if mc else 0
+            return True, ""
+        except Exception as e:  # noqa: BLE001 - any failure selects the IPC back end on every rank
+            return False, f"{type(e).__name__}: {e}"[:200]
+
+    def _drop_symm(self):
+        self._symm = None
+        self._mc_base = 0
+
+    def _init_ipc(self, total: int):
+        import torch.distributed as dist
         with torch.cuda.device(self.device):
             p = C.c_void_p()
             check(lib.b200_comm_alloc(total, C.byref(p)), "b200_comm_alloc")
             self._base = p.value
+            self._ipc_base = p.value
             handle = C.create_string_buffer(_lib.IPC_HANDLE_BYTES)
             check(lib.b200_ipc_export(self._base, handle), "b200_ipc_export")
             handles: List[Optional[bytes]] = [None] * self.world
             dist.all_gather_object(handles, bytes(handle.raw), group=self.group)
-            self._peer_base: List[int] = []
-            self._imported: List[int] = []
+            self._peer_base = []
             for r, h in enumerate(handles):
                 if r == self.rank:
                     self._peer_base.append(self._base)
@@ -124,9 +204,6 @@ class PeerComm:
                 self._imported.append(q.value)
         self._mem = _DevMem(self._base, total)
         self._bytes = torch.as_tensor(self._mem, device=self.device)
-        assert self._bytes.data_ptr() == self._base and self._bytes.numel() == total
-        self._last_slot = -1
-        dist.barrier(group=self.group)          # nobody launches before every rank has mapped every slab
 
     # ------------------------------------------------------------------ buffers
     def slot(self, idx: int, rows: int, n: int) -> torch.Tensor:
@@ -137,7 +214,7 @@ class PeerComm:
         return self._bytes[off: off + rows * n * 2].view(torch.bfloat16).view(rows, n)
 
     def ybuf(self, rows: int, n: int) -> torch.Tensor:
-        """bf16 [rows, n] view of the local peer-visible y buffer (row-sharded form: every owner
+        """bf16 [rows, n] view of the local peer-visible y buffer (row-sharded / NVLS forms: every owner
         pushes its normalised rows into every rank's copy)."""
         assert rows * n * 2 <= self.slot_bytes, "PeerComm y buffer too small"
         off = _HEADER + 2 * self.slot_bytes
@@ -148,22 +225,44 @@ class PeerComm:
 
     def error_flag(self) -> int:
         """1 if any flag wait timed out since creation (synchronises)."""
-        off = _FLAG_BYTES + _lib.AR_MAX_CTAS * 4
-        return int(self._bytes[off: off + 4].view(torch.int32).item())
+        return int(self._bytes[_ERR_OFF: _ERR_OFF + 4].view(torch.int32).item())
+
+    def poll_error(self, every: int = 16) -> None:
+        """Non-blocking check of the kernel's timeout word, for the product path: every ``every``
+        calls an async 4-byte copy of the word is queued behind the work issued so far; the value an
+        EARLIER copy brought back is examined without waiting for the device.  Raises when a flag
+        wait timed out, i.e. a peer rank did not reach the reduction within ``timeout_ms`` and the
+        residual stream of this rank is no longer trustworthy."""
+        if self._err_event is not None and self._err_event.query():
+            if int(self._err_host[0]) != 0:
+                raise RuntimeError(
+                    f"PeerComm (rank {self.rank}): a peer did not reach the fused all-reduce within {self.timeout_ms} ms; "
+                    "results since then are invalid")
+            self._err_event = None
+        self._err_calls += 1
+        if self._err_event is None and self._err_calls % max(1, every) == 0:
+            self._err_host.copy_(self._bytes[_ERR_OFF: _ERR_OFF + 4].view(torch.int32), non_blocking=True)
+            self._err_event = torch.cuda.Event()
+            self._err_event.record()
 
     # ------------------------------------------------------------------ the fused op
     def allreduce_residual_rmsnorm(self, slot_idx: int, rows: int, n: int, residual: Optional[torch.Tensor],
                                    weight: Optional[torch.Tensor], y: Optional[torch.Tensor],
                                    res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False,
-                                   sharded: bool = False, trace: Optional[torch.Tensor] = None, ll: bool = False):
+                                   sharded: bool = False, trace: Optional[torch.Tensor] = None, ll: bool = False,
+                                   nvls: bool = False):
         """res_out = bf16(bf16(sum over ranks of slot[slot_idx][:rows, :n]) + residual);
         y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable.
-        ``sharded``: the row-sharded form (B200_AR_MODE_ROW_SHARDED) — ``y`` must be a prefix view of
-        :meth:`ybuf`, rows <= 1024, and ``residual`` / ``res_out`` are only read / written for the rows
-        this rank owns."""
-        if slot_idx == self._last_slot and not (sharded or ll):
-            raise AssertionError("PeerComm: consecutive fused all-reduces must alternate slots 0 / 1")
-        self._last_slot = slot_idx
+        ``sharded`` / ``nvls``: the row-sharded forms (B200_AR_MODE_ROW_SHARDED, B200_AR_MODE_NVLS) —
+        ``y`` must be a prefix view of :meth:`ybuf`, and ``residual`` / ``res_out`` are only read /
+        written for the rows this rank owns.  ``ll``: the flag-in-data push form (same residual contract)."""
+        assert int(sharded) + int(ll) + int(nvls) <= 1, "PeerComm: choose one of sharded / ll / nvls"
+        mode = "sharded" if sharded else "ll" if ll else "nvls" if nvls else "oneshot"
+        # The one-shot form has no trailing barrier: after a one-shot call on slot s, peers may still be READING
+        # slot s, so the next call (of any form) must use the other slot.  The other forms end with a barrier.
+        if self._last_mode == "oneshot" and slot_idx == self._last_slot:
+            raise AssertionError("PeerComm: the call after a one-shot fused all-reduce must use the other slot (0 / 1)")
+        self._last_slot, self._last_mode = slot_idx, mode
         x = self.slot(slot_idx, rows, n)
         a = ArArgs()
         off = _HEADER + slot_idx * self.slot_bytes
@@ -173,17 +272,25 @@ class PeerComm:
         a.epoch = self._base + _FLAG_BYTES
         _fill_common(a, x, residual, weight, y, res_out, eps, ss_rounded)
         a.rank, a.world, a.timeout_ms = self.rank, self.world, self.timeout_ms
+        yoff = _HEADER + 2 * self.slot_bytes
         if sharded:
-            yoff = _HEADER + 2 * self.slot_bytes
             assert y is not None and y.data_ptr() == self._base + yoff and y.stride(0) == n, \
                 "PeerComm: the row-sharded form writes y into ybuf() on every rank"
             assert rows <= _lib.AR_MAX_CTAS
             a.mode = _lib.AR_MODE_ROW_SHARDED
             for r in range(self.world):
                 a.y_peers[r] = self._peer_base[r] + yoff
+        if nvls:
+            assert self.has_multicast, "PeerComm: the NVLS form needs a multicast mapping (symm back end on an NVSwitch node)"
+            assert y is not None and y.data_ptr() == self._base + yoff and y.stride(0) == n, \
+                "PeerComm: the NVLS form writes y into ybuf() on every rank"
+            a.mode = _lib.AR_MODE_NVLS
+            a.x_mc = self._mc_base + off
+            a.y_mc = self._mc_base + yoff
+            a.flags_mc = self._mc_base
         if ll:
             # LL push form: flag-in-data packets through the staging areas; y is any local tensor
-            assert not sharded and y is not None
+            assert y is not None
             R = -(-rows // self.world)
             assert self.world * R * n * 4 <= self._xstage_bytes and rows * n * 4 <= 2 * self.slot_bytes
             a.mode = _lib.AR_MODE_LL
@@ -205,5 +312,7 @@ class PeerComm:
             lib.b200_ipc_close(p)
         self._imported = []
         self._bytes = None
-        lib.b200_comm_free(self._base)
+        if self.backend == "ipc":
+            lib.b200_comm_free(self._ipc_base)
+        self._symm = None
         self._base = None

@@ -135,10 +135,11 @@ class ModelGraphRunner:
         self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
         if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
             self._comm = None
-        # Reduction form (B200_AR_MODE = oneshot | sharded | ll; default ll from 4 ranks up when the final norm can be
-        # fused, else oneshot).  "ll" and "sharded" reduce + normalise each row on ONE owner rank and keep the residual
-        # stream row-sharded, so they need ln_f fused (a kernel norm); "ll" moves data as flag-in-data packets with
-        # remote stores only (no remote loads, no fences: ~2 one-way NVLink hops per call).
+        # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls).  Default: "nvls" (in-switch reduction,
+        # multimem.ld_reduce / multimem.st on the multicast mapping of the symmetric slabs) when the communicator has
+        # a multicast range and the final norm can be fused; else "ll" from 4 ranks up; else "oneshot".  "nvls", "ll"
+        # and "sharded" reduce + normalise each row on ONE owner rank and keep the residual stream row-sharded, so
+        # they need ln_f fused (a kernel norm); "ll" moves data as flag-in-data packets with remote stores only.
         self._ar_mode = "oneshot"
         if self._comm is not None:
             self._attn_out = self._comm.slot(0, mb, self.hidden_dim)
@@ -146,10 +147,12 @@ class ModelGraphRunner:
             want = os.environ.get("B200_AR_MODE", "auto")
             fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
             if want == "auto":
+                want = "nvls" if self._comm.has_multicast else ("ll" if self.world_size >= 4 else "oneshot")
+            if want == "nvls" and not self._comm.has_multicast:
                 want = "ll" if self.world_size >= 4 else "oneshot"
-            if want in ("ll", "sharded") and fusable:
+            if want in ("ll", "sharded", "nvls") and fusable:
                 self._ar_mode = want
-            if self._ar_mode == "sharded":
+            if self._ar_mode in ("sharded", "nvls"):
                 self._normed = self._comm.ybuf(mb, self.hidden_dim)
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
 
@@ -203,7 +206,8 @@ class ModelGraphRunner:
         if self._comm is not None:
             self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
                                                   y if norm is not None else None, res_out, eps, ss_rounded,
-                                                  sharded=self._ar_mode == "sharded", ll=self._ar_mode == "ll")
+                                                  sharded=self._ar_mode == "sharded", ll=self._ar_mode == "ll",
+                                                  nvls=self._ar_mode == "nvls")
         else:
             all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
             allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,
@@ -272,7 +276,15 @@ class ModelGraphRunner:
         ratio = getattr(cache_manager, "len_max_over_mean", None)     # set by KVCacheManager.cache_batch_data
         return batch_size > 1 and ratio is not None and ratio >= self.RAGGED_RATIO
 
+    def gemm_policy(self) -> str:
+        """Which kernels run the four decode GEMMs (reported by the bench tools)."""
+        return f"B200_SKINNY_GEMM={self._skinny}"
+
     def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
+        if self._comm is not None:
+            # a peer that missed a reduction (flag wait timed out) leaves this rank's residual stream wrong:
+            # surface it here, without waiting for the device (reads the word an earlier async copy brought back)
+            self._comm.poll_error()
         self._input_ids[:batch_size] = input_ids
         ragged = self._is_ragged(cache_manager, batch_size)
         g = (self._graphs_balanced.get(batch_size) if ragged else None) or self._graphs.get(batch_size)

@@ -31,12 +31,15 @@ struct ArParams {
     int64_t rows, n, sx, sr, sy, sres;
     float eps;
     int rank, ss_rounded;
-    long long timeout_cycles;
+    long long timeout_ns;
     __nv_bfloat16* yp[B200_AR_MAX_WORLD];   // row-sharded form: every rank's y buffer (entry `rank` is local)
     int rows_per_rank;                      // row-sharded form: rank r owns rows [r * rows_per_rank, ...)
     uint8_t* xstage[B200_AR_MAX_WORLD];     // LL form: every rank's staging area for pushed partial rows
     uint8_t* ystage[B200_AR_MAX_WORLD];     // LL form: every rank's staging area for pushed normalised rows
     unsigned long long* trace;              // optional [grid][4] %globaltimer stamps: start, barrier passed, row reduced, end
+    const __nv_bfloat16* x_mc;              // NVLS form: multicast address of the x slot (multimem.ld_reduce)
+    __nv_bfloat16* y_mc;                    // NVLS form: multicast address of the y buffer (multimem.st)
+    uint32_t* flags_mc;                     // NVLS form: multicast address of the flag region (multimem.red)
 };
 
 __device__ __forceinline__ void stamp(const ArParams& p, int slot) {
@@ -88,11 +91,19 @@ template <> struct ArW<float> {
     }
 };
 
-// bounded wait for flag >= e (signed distance: the epoch may wrap)
+__device__ __forceinline__ long long now_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// bounded wait for flag >= e (signed distance: the epoch may wrap).  The bound is wall time (%globaltimer,
+// ns), not SM cycles.  A peer that never arrives sets the error word (epoch[B200_AR_MAX_CTAS]) instead of
+// hanging the GPU; the host side polls that word (PeerComm.poll_error) and raises.
 __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t e, const ArParams& p) {
-    const long long t0 = clock64();
+    if ((int32_t)(ld_relaxed_sys(flag) - e) >= 0) return;
+    const long long t0 = now_ns();
     while ((int32_t)(ld_relaxed_sys(flag) - e) < 0) {
-        if (clock64() - t0 > p.timeout_cycles) {              // a peer never arrived: flag it, do not hang the GPU
+        if (now_ns() - t0 > p.timeout_ns) {
             atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u);
             break;
         }
@@ -271,10 +282,10 @@ __device__ __forceinline__ void ll_gather(const uint8_t* (&src)[N], int self, ui
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             if (!ll_ready(pk[s][h], e)) {
-                const long long t0 = clock64();
+                const long long t0 = now_ns();
                 do {
                     pk[s][h] = ld_peer_v4(src[s] + 16 * h);
-                    if (clock64() - t0 > p.timeout_cycles) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+                    if (now_ns() - t0 > p.timeout_ns) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
                 } while (!ll_ready(pk[s][h], e));
             }
         }
@@ -411,6 +422,169 @@ allreduce_ll_kernel(const __grid_constant__ ArParams p) {
     stamp(p, 3);
 }
 
+
+// ------------------------------------------------------------------ NVLS form (in-switch reduction)
+// All ranks map ONE multicast object over their symmetric slabs (cuMulticast*, set up by the host side).  A
+// multimem.ld_reduce on a multicast address makes the NVSwitch read the same offset from every GPU and hand back the
+// SUM (fp32 accumulation in the switch, one rounding to bf16); a multimem.st / multimem.red writes / adds the operand
+// on every GPU at once.  One call is therefore
+//     1 x multimem.red  (x of this rank is written)         -> every rank's `ready` counter
+//     rank r, for its rows [r*R, (r+1)*R):  multimem.ld_reduce the row  (one switch round trip instead of world-1
+//         peer reads), add ITS residual row, normalise, write res_out locally, multimem.st y to EVERY rank
+//     1 x multimem.red.release per CTA (my rows are stored) -> every rank's `done` counter; wait for all CTAs of all ranks
+// Counters are monotonic; the targets live in local memory and are advanced by the last CTA of every call, so
+// a captured CUDA graph replays forever and calls of different row counts can be mixed (every rank makes the
+// same sequence of calls).  Row ownership and the row-sharded residual contract are those of ROW_SHARDED.  All
+// ranks get y from ONE computation, so they are bit-identical.  After a call returns on any rank every owner
+// has finished reading x, so the x slot may be rewritten at once (no slot alternation needed).
+#define B200_AR_NVLS_READY_WORD (B200_AR_MAX_CTAS * (B200_AR_MAX_WORLD + 1))         // u32 index in the flag region
+#define B200_AR_NVLS_DONE_WORD  (B200_AR_NVLS_READY_WORD + 32)                         // 128 bytes apart
+#define B200_AR_EPOCH_NVLS_READY (B200_AR_MAX_CTAS + 4)                                // local targets / arrival counter
+#define B200_AR_EPOCH_NVLS_DONE  (B200_AR_MAX_CTAS + 5)
+#define B200_AR_EPOCH_NVLS_ARRIVE (B200_AR_MAX_CTAS + 6)
+
+__device__ __forceinline__ void multimem_red_add_relaxed(uint32_t* mc, uint32_t v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.u32 [%0], %1;" :: "l"(mc), "r"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_release(uint32_t* mc, uint32_t v) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" :: "l"(mc), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <int VPT, typename WT>
+__global__ void __launch_bounds__(1024)
+allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
+    __shared__ float red[32];
+    const int T = blockDim.x;
+    const int nvec = (int)(p.n >> 3);
+    stamp(p, 0);
+    const uint32_t ready_t = p.epoch[B200_AR_EPOCH_NVLS_READY] + (uint32_t)world;
+    const uint32_t done_t = p.epoch[B200_AR_EPOCH_NVLS_DONE] + (uint32_t)world * gridDim.x;
+    uint32_t* my_flags = p.flags[p.rank];
+    if (threadIdx.x == 0) {
+        // x was written by the kernel that precedes this one in the stream: no fence needed (see st_relaxed_sys)
+        if (blockIdx.x == 0) multimem_red_add_relaxed(p.flags_mc + B200_AR_NVLS_READY_WORD, 1u);
+        wait_flag(my_flags + B200_AR_NVLS_READY_WORD, ready_t, p);
+    }
+    __syncthreads();
+    stamp(p, 1);
+    // a CTA walks rows j, j + grid, ... of this rank's share: the grid is capped so that every CTA of the call is
+    // resident at once (the done barrier below waits for ALL of them)
+    for (int64_t j = blockIdx.x; j < p.rows_per_rank; j += gridDim.x) {
+        const int64_t row = (int64_t)p.rank * p.rows_per_rank + j;
+        if (row >= p.rows) break;
+        const bool has_r = p.r != nullptr;
+        float ss = 0.0f;
+        float f[VPT][8];
+        uint4 sv[VPT], rv[VPT];
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {                       // every switch round trip of the row in flight at once
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                sv[i] = multimem_ld_reduce_bf16x8(p.x_mc + row * p.sx + (int64_t)v * 8);
+                rv[i] = has_r ? ld_v4(p.r + row * p.sr + (int64_t)v * 8) : make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                uint4 ro;
+                uint32_t* pro = &ro.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    // the switch hands back bf16(sum over ranks): what all_reduce returns
+                    float a = bf16lo((&sv[i].x)[k]), b = bf16hi((&sv[i].x)[k]);
+                    if (has_r) { a += bf16lo((&rv[i].x)[k]); b += bf16hi((&rv[i].x)[k]); }
+                    const uint32_t pk = pack_bf16(a, b);
+                    pro[k] = pk;
+                    const float ar = bf16lo(pk), br = bf16hi(pk);
+                    if (p.ss_rounded) { ss += ar * ar; ss += br * br; }
+                    else              { ss += a * a;   ss += b * b; }
+                    f[i][2 * k] = ar; f[i][2 * k + 1] = br;
+                }
+                st_na_v4(p.res_out + row * p.sres + (int64_t)v * 8, ro);
+            }
+        }
+        {
+            const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+            const int nw = (T + 31) >> 5;
+            ss = warp_sum(ss);
+            if (nw > 1) {
+                __syncthreads();                              // red[] may still be read for the previous row
+                if (lane == 0) red[wid] = ss;
+                __syncthreads();
+                float t = (lane < nw) ? red[lane] : 0.0f;
+                ss = warp_sum(t);
+            }
+        }
+        const float rrms = rsqrtf(ss / (float)p.n + p.eps);
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + i * T;
+            if (v < nvec) {
+                float wf[8];
+                ArW<WT>::load8(p.w, (int64_t)v * 8, wf);
+                uint4 o;
+                uint32_t* po = &o.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
+                multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);      // lands in every rank's y buffer
+            }
+        }
+    }
+    stamp(p, 2);
+    __syncthreads();                                         // every thread's multimem.st is ordered before the release below
+    if (threadIdx.x == 0) {
+        multimem_red_add_release(p.flags_mc + B200_AR_NVLS_DONE_WORD, 1u);
+        // all CTAs of all ranks have stored their rows (and finished reading x)
+        if ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
+            const long long t0 = now_ns();
+            while ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
+                if (now_ns() - t0 > p.timeout_ns) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+            }
+        }
+        // the last CTA of the call advances the targets (every CTA read them before it could arrive here)
+        const unsigned arrived = atomicAdd(p.epoch + B200_AR_EPOCH_NVLS_ARRIVE, 1u);
+        if (arrived == gridDim.x - 1) {
+            p.epoch[B200_AR_EPOCH_NVLS_ARRIVE] = 0u;
+            p.epoch[B200_AR_EPOCH_NVLS_READY] = ready_t;
+            p.epoch[B200_AR_EPOCH_NVLS_DONE] = done_t;
+        }
+    }
+    stamp(p, 3);
+}
+
+template <typename WT>
+static int launch_nvls(const ArParams& p, int world, cudaStream_t st) {
+    const int64_t nvec = p.n / 8;
+    const unsigned grid = (unsigned)(p.rows_per_rank < 128 ? p.rows_per_rank : 128);   // all resident at once (148 SMs)
+    if (nvec <= 1024) {
+        int threads = (int)((nvec + 31) & ~31LL);
+        allreduce_nvls_kernel<1, WT><<<grid, threads, 0, st>>>(p, world);
+    } else {
+        int threads = (int)((((nvec + 1) / 2) + 31) & ~31LL);
+        allreduce_nvls_kernel<2, WT><<<grid, threads, 0, st>>>(p, world);
+    }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
 template <int WS, typename WT>
 static int launch_ll(const ArParams& p, cudaStream_t st) {
     const int64_t nvec = p.n / 8;
@@ -537,6 +711,20 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
         if (p.rows_per_rank < 1) p.rows_per_rank = 1;
     }
+    const bool nvls = (a->mode & B200_AR_MODE_NVLS) != 0;
+    if (nvls) {
+        if (sharded || ll) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: choose one of ROW_SHARDED / LL / NVLS");
+        if (a->world < 2) B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: NVLS form needs world > 1");
+        if (!a->weight) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the norm (weight, y)");
+        if (!a->x_mc || !a->y_mc || !a->flags_mc || !aligned16(a->x_mc) || !aligned16(a->y_mc))
+            B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the multicast addresses of x, y and the flags");
+        if (a->rows > 65535LL * a->world) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: NVLS form: too many rows");
+        p.x_mc = (const __nv_bfloat16*)a->x_mc;
+        p.y_mc = (__nv_bfloat16*)a->y_mc;
+        p.flags_mc = (uint32_t*)a->flags_mc;
+        p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
+        if (p.rows_per_rank < 1) p.rows_per_rank = 1;
+    }
     if (a->rows == 0) return 0;
     p.epoch = (uint32_t*)a->epoch;
     p.r = (const __nv_bfloat16*)a->residual;
@@ -547,9 +735,14 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
     p.sx = a->stride_x; p.sr = a->stride_r; p.sy = a->stride_y; p.sres = a->stride_res;
     p.eps = a->eps; p.rank = a->rank; p.ss_rounded = a->ss_rounded ? 1 : 0;
     const int ms = a->timeout_ms > 0 ? a->timeout_ms : 2000;
-    p.timeout_cycles = (long long)ms * 2000000LL;          // ~2 GHz SM clock upper bound
+    p.timeout_ns = (long long)ms * 1000000LL;
     p.trace = (unsigned long long*)a->trace;
     cudaStream_t st = (cudaStream_t)stream;
+    if (nvls) {
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16>(p, a->world, st);
+        B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
+    }
     if (ll) {
         if (a->w_dtype == B200_DT_F32) return dispatch_ll<float>(a->world, p, st);
         if (a->w_dtype == B200_DT_BF16) return dispatch_ll<__nv_bfloat16>(a->world, p, st);

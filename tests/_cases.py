@@ -50,17 +50,29 @@ def to_dev(case, dev="cuda"):
     return {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in case.items()}
 
 
-def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_frac=3e-4, tail_scale=5.0):
+# Every assert_close call leaves a record here; tests/conftest.py writes them to
+# gpurun_out/parity_tail.json at session end (committed per round as profiles/rNN/parity_tail.json),
+# so the size of the tolerance tail that the CUDA kernels actually use is on file.
+PARITY_LOG = []
+
+# Tail allowance, pinned to what was MEASURED on the B200 over the whole GPU suite
+# (profiles/r02/parity_tail.json): see the docstring of assert_close.
+TAIL_FRAC = 3e-4
+TAIL_SCALE = 5.0
+
+
+def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_frac=None, tail_scale=None):
     """north_star tolerance against the fp32 oracle: |a - e| <= 2e-3 + 1e-2 * |e|.
 
     Attention probabilities enter the P.V tensor-core product as bf16 (8-bit mantissa) — in this
     kernel exactly as in flash-attn — so an output that is a near-cancelling sum of O(1) terms
-    can miss the bound by a few 1e-3.  Measured on the B200 with the library the reference calls
-    (tests/golden/make_golden_gpu.py, gpurun_out/golden_gpu.log): flash-attn 2.8.3 itself leaves
-    1 of 614 400 prefill outputs at 9.9e-3 against this oracle.  The bar is therefore: every
-    element inside the bound, except a tail of at most max(2, 3e-4 * numel) elements which must
-    still be inside 5x the bound; anything systematic (a wrong page, a wrong rotation, a missed
-    token) produces O(0.1 - 1) errors on many elements and fails both clauses."""
+    can miss the bound by a few 1e-3.  The bar is: every element inside the bound, except a tail
+    of at most max(2, TAIL_FRAC * numel) elements which must still be inside TAIL_SCALE x the
+    bound; anything systematic (a wrong page, a wrong rotation, a missed token) produces
+    O(0.1 - 1) errors on many elements and fails both clauses.  Returns (n_out_of_bound,
+    worst err / bound) and logs them (PARITY_LOG)."""
+    tail_frac = TAIL_FRAC if tail_frac is None else tail_frac
+    tail_scale = TAIL_SCALE if tail_scale is None else tail_scale
     a = actual.float().cpu()
     e = expected_f32.float().cpu()
     assert a.shape == e.shape, f"{what}: shape {tuple(a.shape)} vs {tuple(e.shape)}"
@@ -70,7 +82,12 @@ def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_fr
     n_bad = int(bad.sum())
     allowed = max(2, int(tail_frac * bad.numel()))
     worst = float((err / lim).max()) if bad.numel() else 0.0
+    import os
+    PARITY_LOG.append({"test": os.environ.get("PYTEST_CURRENT_TEST", "").split(" ")[0], "what": what,
+                       "numel": int(bad.numel()), "out_of_bound": n_bad, "worst_err_over_bound": round(worst, 3),
+                       "max_abs_err": float(err.max()) if bad.numel() else 0.0, "allowed_tail": allowed})
     assert n_bad <= allowed and worst <= tail_scale, (
         f"{what}: {n_bad}/{bad.numel()} elements out of tolerance (allowed tail {allowed}), "
         f"max abs err {float(err.max()):.4e}, worst err/bound {worst:.2f}"
         + (f" at {tuple(torch.nonzero(bad)[0].tolist())}" if n_bad else ""))
+    return n_bad, worst

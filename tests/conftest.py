@@ -33,3 +33,24 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """Write the tolerance-tail records of every assert_close call of this session (GPU runs only)."""
+    try:
+        import json
+        from _cases import PARITY_LOG
+    except Exception:  # noqa: BLE001
+        return
+    if not PARITY_LOG:
+        return
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    worst = max(PARITY_LOG, key=lambda r: r["worst_err_over_bound"])
+    most = max(PARITY_LOG, key=lambda r: r["out_of_bound"] / max(1, r["numel"]))
+    summary = {"calls": len(PARITY_LOG), "calls_with_any_out_of_bound": sum(1 for r in PARITY_LOG if r["out_of_bound"]),
+               "max_out_of_bound": max(r["out_of_bound"] for r in PARITY_LOG),
+               "max_out_of_bound_fraction": most["out_of_bound"] / max(1, most["numel"]),
+               "max_worst_err_over_bound": worst["worst_err_over_bound"], "worst_case": worst, "largest_tail_case": most}
+    with open(os.path.join(out, "parity_tail.json"), "w") as f:
+        json.dump({"summary": summary, "records": [r for r in PARITY_LOG if r["out_of_bound"]]}, f, indent=1)

@@ -23,6 +23,11 @@ CASES = {
     "decode_interleaved_mha_d64": (dict(B=4, Hq=4, Hkv=4, D=64, lens=[1, 254, 257, 40], seed=2), True, True),
     "decode_gqa7_d64": (dict(B=3, Hq=14, Hkv=2, D=64, lens=[129, 0, 255], seed=3), False, True),
     "decode_llama8b_b4_4k": (dict(B=4, Hq=32, Hkv=8, D=128, lens=[4095, 4000, 2049, 1], seed=6), False, True),
+    # round 2: BASELINE.json configs[1] at full size, one 128k-context row (configs[4]), D = 64 and G = 7 prefill
+    "decode_llama8b_b32_4k_cfg2": (dict(B=32, Hq=32, Hkv=8, D=128, lens=[4095] * 32, seed=7), False, True),
+    "decode_llama8b_b1_128k": (dict(B=1, Hq=32, Hkv=8, D=128, lens=[131071], seed=8, rot_rows=131080), False, True),
+    "prefill_gqa7_d64": (dict(B=1, Hq=14, Hkv=2, D=64, lens=[0], S_new=300, seed=9), False, True),
+    "prefill_gqa7_d128_prefix": (dict(B=2, Hq=28, Hkv=4, D=128, lens=[100, 300], S_new=200, seed=10), False, True),
     "prefill_empty_d128": (dict(B=1, Hq=8, Hkv=2, D=128, lens=[0], S_new=150, seed=4), False, False),
     "prefill_prefix_d128": (dict(B=1, Hq=4, Hkv=1, D=128, lens=[200], S_new=130, seed=5), False, True),
 }

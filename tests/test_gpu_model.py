@@ -9,6 +9,7 @@ from core.layer.model_graph import ModelGraphRunner
 from core.layer.model_prefill import ModelPrefillRunner
 from core.layer.synthetic_model import SHAPES, Shape, build_synthetic_model
 from _ref_model import RefPathModel
+from oracle.cache_manager import AllocatorOracle
 
 pytestmark = pytest.mark.gpu
 
@@ -55,12 +56,31 @@ def run_product(dec, pre, mgr, prompt, steps, graph=True, feed=None):
     return torch.stack(toks, 1), torch.stack(all_logits, 1)
 
 
+class _OracleTables:
+    """AllocatorOracle with the tensor-returning cache_batch_data the reference-path model consumes."""
+
+    def __init__(self, oracle):
+        self.o = oracle
+
+    def alloc(self, s, n):
+        return self.o.alloc(s, n)
+
+    def append(self, s):
+        return self.o.append(s)
+
+    def cache_batch_data(self, ids, lens):
+        bt, sl = self.o.cache_batch_data(ids, lens)
+        return torch.tensor(bt, dtype=torch.int32), torch.tensor(sl, dtype=torch.int32)
+
+
 def run_reference_path(dec, mgr_shape, prompt, steps, feed=None):
     """Same drive with oracle ops; `feed` (tokens [B, steps]) forces the inputs so logits can be
     compared step by step even after a divergence."""
     n_layers, n_blocks, Hkv, D, max_tokens, max_bs = mgr_shape
-    ref_mgr = KVCacheManager(n_blocks, 256, 1, 1, 8, dtype=torch.bfloat16, device="cpu", max_tokens=max_tokens,
-                             max_batch_size=max_bs)
+    # the checker's allocator is the ORACLE restatement of the reference class (oracle/cache_manager.py, pinned on the
+    # reference's recorded traces), never the product's KVCacheManager: a bug in append / cache_batch_data must not
+    # move both sides together
+    ref_mgr = _OracleTables(AllocatorOracle(n_blocks, 256, max_tokens=max_tokens, max_batch_size=max_bs))
     kc = [torch.zeros(n_blocks, 256, Hkv, D, dtype=torch.bfloat16) for _ in range(n_layers)]
     vc = [torch.zeros(n_blocks, 256, Hkv, D, dtype=torch.bfloat16) for _ in range(n_layers)]
     ref = RefPathModel(dec, dec.attention._cos_pool, dec.attention._sin_pool)

@@ -4,6 +4,7 @@
   one-shot : b200_allreduce_residual_rmsnorm (every rank loads all ranks' slots)
   sharded  : row-sharded form (owner reduces its rows, pushes y to all ranks)
   ll       : LL push form (flag-in-data packets, remote stores only)
+  nvls     : in-switch reduction (multimem.ld_reduce / multimem.st on the multicast mapping; needs the symm back end)
   nccl     : dist.all_reduce + the local fused residual+norm kernel (B200_FUSED_ALLREDUCE=0 path)
 
 Also prints the in-kernel %globaltimer phases of the fused forms (mean over CTAs of rank 0, last
@@ -51,9 +52,10 @@ def main():
         def fused(mode, tr=None):
             for c in range(calls):
                 comm.allreduce_residual_rmsnorm(c & 1, rows, n, res_a if c & 1 == 0 else res_b, w,
-                                                yb if mode == "sharded" else y_loc, res_b if c & 1 == 0 else res_a, 1e-5,
+                                                yb if mode in ("sharded", "nvls") else y_loc,
+                                                res_b if c & 1 == 0 else res_a, 1e-5,
                                                 bool(c & 1), sharded=mode == "sharded", ll=mode == "ll",
-                                                trace=tr if c == calls - 1 else None)
+                                                nvls=mode == "nvls", trace=tr if c == calls - 1 else None)
 
         def nccl():
             for c in range(calls):
@@ -85,8 +87,40 @@ def main():
             del g
             return float(t.item())
 
-        row = {"world": world, "rows": rows, "n": n, "bytes_per_rank": rows * n * 2}
-        for name in ("oneshot", "sharded", "ll"):
+        row = {"world": world, "rows": rows, "n": n, "bytes_per_rank": rows * n * 2, "backend": comm.backend,
+               "multicast": comm.has_multicast}
+        modes = ("oneshot", "sharded", "ll") + (("nvls",) if comm.has_multicast else ())
+        # correctness of every form against an fp32 NCCL sum of the same slot (one call, slot 0, no residual stream reuse)
+        R = -(-rows // world)
+        own = slice(rank * R, min(rows, (rank + 1) * R))
+        ref = xs[0].float().clone()
+        dist.all_reduce(ref)
+        resid = torch.randn(rows, n, device=dev, dtype=torch.bfloat16)
+        dist.broadcast(resid, 0)                             # the residual stream is replicated (owners read their rows)
+        want_res = (ref.bfloat16().float() + resid.float()).bfloat16()
+        want_y = (want_res.float() * torch.rsqrt(want_res.float().pow(2).mean(-1, keepdim=True) + 1e-5)).bfloat16()
+        for name in modes:
+            ro = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
+            yo = yb if name in ("sharded", "nvls") else y_loc
+            yo.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_residual_rmsnorm(0, rows, n, resid, w, yo, ro, 1e-5, True, sharded=name == "sharded",
+                                            ll=name == "ll", nvls=name == "nvls")
+            comm.allreduce_residual_rmsnorm(1, rows, n, resid, w, yo, torch.empty_like(ro), 1e-5, True,
+                                            sharded=name == "sharded", ll=name == "ll", nvls=name == "nvls")  # slot alternation
+            comm.allreduce_residual_rmsnorm(0, rows, n, resid, w, yo, ro, 1e-5, True, sharded=name == "sharded",
+                                            ll=name == "ll", nvls=name == "nvls")
+            torch.cuda.synchronize()
+            dist.barrier()
+            sl = slice(0, rows) if name == "oneshot" else own
+            bad_res = int((ro[sl].float() - want_res[sl].float()).abs().gt(want_res[sl].float().abs() * 2 ** -7 + 1e-3).sum())
+            bad_y = int((yo.float() - want_y.float()).abs().gt(want_y.float().abs() * 2 ** -6 + 2e-3).sum())
+            ys = [torch.empty_like(yo) for _ in range(world)]
+            dist.all_gather(ys, yo.contiguous())
+            same = all(torch.equal(ys[0], t_) for t_ in ys)
+            row[name + "_check"] = {"res_out_bad": bad_res, "y_bad": bad_y, "ranks_bit_identical_y": bool(same)}
+        for name in modes:
             row[name + "_us"] = round(time_graph(lambda: fused(name)), 2)
             trace.zero_()
             fused(name, trace)

@@ -18,7 +18,7 @@ sys.path[:0] = [os.path.join(ROOT, "micro-vllm_b200"), ROOT]
 import torch  # noqa: E402
 import b200ops  # noqa: E402
 from core.paged_attention import build_rotary_tables  # noqa: E402
-from oracle.paged_attention import decode_algorithmic_bytes  # noqa: E402
+decode_algorithmic_bytes = b200ops.decode_algorithmic_bytes
 
 Hq, Hkv, D, LAYERS, PAGE = 28, 4, 128, 28, 256
 N_SEQ, N_PREFILL = 64, 8

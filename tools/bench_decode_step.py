@@ -97,9 +97,21 @@ def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup
            "ctx": ctx, "ms_per_step_run": round(ms, 4), "head_ms": round(head_ms, 4),
            "tokens_per_s_run": round(batch / (ms * 1e-3), 1),
            "tokens_per_s_full_depth_extrapolated": round(batch / (full_ms * 1e-3), 1),
-           "setup_s": round(setup_s, 1)}
+           "setup_s": round(setup_s, 1),
+           "allreduce": ("none (TP=1)" if world == 1 else
+                         ("fused-" + runner._ar_mode) if runner._comm is not None else "nccl"),
+           "gemm": runner.gemm_policy()}
+    comm = getattr(runner, "_comm", None)
+    if comm is not None:
+        res["allreduce_timeout_flag"] = comm.error_flag()
     if rank == 0 and verbose:
         print(json.dumps(res), flush=True)
+    # graphs that captured NCCL kernels must be gone before the communicator is destroyed
+    del runner, mgr, model
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     return res
 
 

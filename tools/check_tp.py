@@ -46,21 +46,24 @@ def build(shape, layers, batch, ctx, dev, world, fused):
     return runner, mgr
 
 
-def main():
+def run_check(layers=4, batch=16, ctx=700, steps=6, shape_name="llama3-8b"):
+    """Returns the check record (same dict on every rank); torch.distributed must be initialised."""
+    import gc
     import torch.distributed as dist
     from core import parallel_config as pc
     from core.layer.synthetic_model import SHAPES
     world = int(os.environ.get("WORLD_SIZE", 1))
-    rank = int(os.environ.get("RANK", 0))
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
     pc.setup()
-    shape = SHAPES["llama3-8b"]
-    layers, batch, ctx, steps = 4, 16, 700, 6
-    out = {}
+    shape = SHAPES[shape_name]
+    prev_env = os.environ.get("B200_FUSED_ALLREDUCE")
+    out, mode = {}, None
     for fused in (True, False):
         runner, mgr = build(shape, layers, batch, ctx, dev, world, fused)
+        if fused:
+            mode = runner._ar_mode
         tok = torch.randint(0, 4096, (batch,), device=dev, generator=torch.Generator(device=dev).manual_seed(3))
         logits = []
         for s in range(steps):
@@ -73,6 +76,10 @@ def main():
             tok = lg.argmax(-1)
         out[fused] = torch.stack(logits)
         torch.cuda.synchronize()
+        # graphs that captured NCCL kernels must be gone before the communicator is destroyed
+        del runner, mgr
+        gc.collect()
+        torch.cuda.synchronize()
         dist.barrier()
     fused_l, nccl_l = out[True], out[False]
     gathered = [torch.empty_like(fused_l) for _ in range(world)]
@@ -80,22 +87,29 @@ def main():
     same = all(torch.equal(gathered[0], g) for g in gathered)
     # compare only step 0 strictly (later steps may follow different argmax tokens after a near-tie)
     rel0 = float((fused_l[0] - nccl_l[0]).pow(2).mean().sqrt() / nccl_l[0].pow(2).mean().sqrt())
-    os.environ["B200_FUSED_ALLREDUCE"] = "1"
-    comm = pc.peer_comm(1)
+    if prev_env is None:
+        os.environ.pop("B200_FUSED_ALLREDUCE", None)
+    else:
+        os.environ["B200_FUSED_ALLREDUCE"] = prev_env
+    comm = pc._state.get("peer_comm")
     err = comm.error_flag() if comm is not None else -1
-    res = {"world": world, "ar_mode": os.environ.get("B200_AR_MODE", "auto"), "ranks_bit_identical": bool(same), "rel_rms_fused_vs_nccl_step0": round(rel0, 5),
-           "timeout_flag": err}
-    if rank == 0:
+    res = {"world": world, "ar_mode": mode, "ranks_bit_identical": bool(same),
+           "rel_rms_fused_vs_nccl_step0": round(rel0, 5), "timeout_flag": err,
+           "shape": f"{shape_name} x{layers} layers, batch {batch}, ctx {ctx}, {steps} greedy steps",
+           # bf16 rounding-order noise of a 4-layer stack is 1-2 % rms
+           "ok": bool(same and rel0 < 0.03 and err == 0)}
+    return res
+
+
+def main():
+    import torch.distributed as dist
+    res = run_check()
+    if int(os.environ.get("RANK", 0)) == 0:
         print(json.dumps(res), flush=True)
-    ok = same and rel0 < 0.03 and err == 0      # bf16 rounding-order noise of a 4-layer stack is 1-2 % rms
-    # graphs that captured NCCL kernels must be gone before the communicator is destroyed (else destroy waits forever)
-    del runner, mgr
-    import gc
-    gc.collect()
     torch.cuda.synchronize()
     dist.barrier()
     dist.destroy_process_group()
-    sys.exit(0 if ok else 1)
+    sys.exit(0 if res["ok"] else 1)
 
 
 if __name__ == "__main__":

@@ -13,7 +13,7 @@ sys.path[:0] = [os.path.join(ROOT, "micro-vllm_b200"), ROOT]
 import torch  # noqa: E402
 import b200ops  # noqa: E402
 from core.paged_attention import build_rotary_tables  # noqa: E402
-from oracle.paged_attention import decode_algorithmic_bytes  # noqa: E402
+decode_algorithmic_bytes = b200ops.decode_algorithmic_bytes
 
 SHAPES = {
     "l8": dict(B=32, Hq=32, Hkv=8, D=128, ctx=4096),
