@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 12
+#define B200_ABI_VERSION 13
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -121,7 +121,40 @@ int b200_greedy_argmax(const void* logits, int logits_dtype,
                        void* stream);
 
 /* ------------------------------------------------------------------------ *
- * Weight-streaming GEMM for decode-sized batches — replaces the torch.matmul
+ * Weight-streaming GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, swap-AB:
+ * the weights are the 128-row UMMA M operand, the batch is the UMMA N) — replaces the
+ * torch.matmul (cuBLAS) calls of a decode layer AND the elementwise launches behind them:
+ * core/layer/model_graph.py:145-147 (QKV projection + bias add, B200_GEMM_EPI_BIAS), :171
+ * (o_proj), :183-184 (gate_up projection + kernel/swiglu.py::swiglu_gemm,
+ * B200_GEMM_EPI_SWIGLU), :185 (down_proj).  SURVEY.md §8f N4.
+ *   out[m, n] = bf16( sum_k f32(x[m, k]) * f32(w[n, k]) )                 (fp32 accumulate)
+ *   EPI_BIAS:   out = bf16( f32(bf16(sum)) + f32(bias[n]) )               (two roundings, like the reference)
+ *   EPI_SWIGLU: w rows are interleaved (row 2j = up_j, row 2j+1 = gate_j);
+ *               out[m, j] = bf16( silu(f32(bf16(gate))) * f32(bf16(up)) ), out is [M, N/2]
+ * x [M, K] bf16, 1 <= M <= 128; w [N, K] bf16 (nn.Linear layout, K contiguous); K % 64 == 0,
+ * N % 8 == 0; strides in elements (ldx, ldw multiples of 8; ldo multiple of 4).  HBM-bound on w.
+ * One persistent CTA per SM, the (128-row tile, 64-element k-block) units dealt out in equal
+ * contiguous shares (stream-K); tiles shared between CTAs are reduced by all of them in fixed
+ * order (deterministic).  workspace: b200_stream_gemm_workspace_bytes(M, N, grid_hint) bytes,
+ * 16-byte aligned, ZERO-FILLED ONCE by the caller; the kernel leaves its counters zeroed
+ * (replay safe).  grid_hint: 0 = one CTA per SM (never more: the CTAs wait on one another).
+ * flags: B200_GEMM_FLAG_PDL launches with programmatic stream serialization: the first weight
+ * boxes are requested before griddepcontrol.wait (precondition: the preceding kernel in the
+ * stream writes neither w nor bias).
+ * ------------------------------------------------------------------------ */
+#define B200_GEMM_EPI_NONE   0
+#define B200_GEMM_EPI_BIAS   1
+#define B200_GEMM_EPI_SWIGLU 2
+#define B200_GEMM_FLAG_PDL   1
+int64_t b200_stream_gemm_workspace_bytes(int M, int64_t N, int grid_hint);
+int b200_stream_gemm(const void* x, const void* w, const void* bias, void* out,
+                     void* workspace, int64_t workspace_bytes,
+                     int M, int64_t K, int64_t N, int64_t ldx, int64_t ldw, int64_t ldo,
+                     int epilogue, int flags, int grid_hint, void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Weight-streaming GEMM for decode-sized batches (legacy mma.sync form, kept for the
+ * [in, out] weight layout) — replaces the torch.matmul
  * (cuBLAS) calls of a decode layer: core/layer/model_graph.py:145-147 (QKV
  * projection; `bias` reproduces the separate bf16 add), :171 (o_proj), :183
  * (gate_up), :185 (down_proj), on the [in, out]-contiguous weights of

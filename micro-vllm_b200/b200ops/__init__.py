@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "decode_num_splits", "decode_use_balanced", "decode_algorithmic_bytes", "reserve_graph_workspace", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "stream_gemm", "stream_gemm_ok", "interleave_up_gate", "decode_num_splits", "decode_use_balanced", "decode_algorithmic_bytes", "reserve_graph_workspace", "B200Error", "LIB_PATH",
 ]
 
 
@@ -366,7 +366,61 @@ def greedy_argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
     return out[:rows]
 
 
-# ------------------------------------------------------------------ decode-sized GEMM
+# ------------------------------------------------------------------ decode-sized GEMM (tcgen05)
+STREAM_MAX_M = 128
+
+
+def stream_gemm_ok(m: int, k: int, n: int) -> bool:
+    """Shapes ``b200_stream_gemm`` accepts (1..128 rows, K % 64 == 0, N % 8 == 0)."""
+    return 1 <= m <= STREAM_MAX_M and k >= 64 and k % 64 == 0 and n >= 8 and n % 8 == 0
+
+
+def interleave_up_gate(up_w: torch.Tensor, gate_w: torch.Tensor) -> torch.Tensor:
+    """Weight layout of the fused gate_up + SwiGLU product: rows ``2j`` / ``2j + 1`` = ``up_w[j]`` / ``gate_w[j]``
+    (both ``[d, K]``, nn.Linear layout); the pair of an output column then sits in adjacent TMEM lanes."""
+    assert up_w.shape == gate_w.shape and up_w.dim() == 2
+    return torch.stack([up_w, gate_w], dim=1).reshape(2 * up_w.shape[0], up_w.shape[1]).contiguous()
+
+
+def stream_gemm(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None,
+                bias: Optional[torch.Tensor] = None, swiglu: bool = False, pdl: bool = False,
+                grid: int = 0) -> torch.Tensor:
+    """out = x @ w.T (+ bias | SwiGLU): x [M, K] bf16 with M <= 128, w [N, K] bf16 (the nn.Linear layout).
+    Streams ``w`` once at HBM speed on tcgen05 tensor cores (TMA ring, TMEM accumulators, stream-K over one
+    persistent CTA per SM, deterministic); capturable.  ``bias`` is added as a second bf16 rounding like the
+    reference's separate ``qkv + bias`` (core/layer/model_graph.py:147).  ``swiglu``: ``w`` is the interleaved
+    up/gate matrix of :func:`interleave_up_gate` and ``out [M, N/2] = silu(gate) * up`` with the rounding points
+    of ``matmul`` -> ``swiglu_gemm`` (:183-184).  ``pdl``: programmatic dependent launch (the kernel before this
+    one in the stream must not write ``w`` / ``bias``)."""
+    _req_cuda(x, w, out, bias)
+    assert x.dim() == 2 and w.dim() == 2 and x.shape[1] == w.shape[1], "stream_gemm: x [M, K] @ w [N, K]^T"
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16, "stream_gemm: bf16 only"
+    M, K = x.shape
+    N = w.shape[0]
+    assert stream_gemm_ok(M, K, N), f"stream_gemm: unsupported shape M={M} K={K} N={N}"
+    assert x.stride(1) == 1 and w.stride(1) == 1
+    assert not (swiglu and bias is not None), "stream_gemm: one epilogue at a time"
+    n_out = N // 2 if swiglu else N
+    if swiglu:
+        assert N % 16 == 0
+    if out is None:
+        out = torch.empty((M, n_out), dtype=torch.bfloat16, device=x.device)
+    assert out.dtype == torch.bfloat16 and out.shape == (M, n_out) and out.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.is_contiguous() and bias.numel() == N
+    with torch.cuda.device(x.device):
+        need = int(lib.b200_stream_gemm_workspace_bytes(M, N, int(grid)))
+    ws = _workspace(x.device, need, "sgemm")
+    epi = _lib.GEMM_EPI_SWIGLU if swiglu else (_lib.GEMM_EPI_BIAS if bias is not None else _lib.GEMM_EPI_NONE)
+    check(lib.b200_stream_gemm(x.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None,
+                               out.data_ptr(), ws.data_ptr(), ws.numel(), M, K, N,
+                               x.stride(0) if M > 1 else max(x.stride(0), K), w.stride(0),
+                               out.stride(0) if M > 1 else max(out.stride(0), n_out),
+                               epi, _lib.GEMM_FLAG_PDL if pdl else 0, int(grid), _stream()), "b200_stream_gemm")
+    return out
+
+
+# ------------------------------------------------------------------ decode-sized GEMM (legacy mma.sync form)
 SKINNY_MAX_M = 64
 
 

@@ -23,7 +23,7 @@ INCLUDE = os.path.join(os.path.dirname(ROOT), "include")
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(HERE, "libb200ops.so")
 
-SOURCES = ["elementwise.cu", "decode_attn.cu", "prefill_attn.cu", "allreduce_norm.cu", "sampling.cu", "skinny_gemm.cu"]
+SOURCES = ["elementwise.cu", "decode_attn.cu", "prefill_attn.cu", "allreduce_norm.cu", "sampling.cu", "skinny_gemm.cu", "stream_gemm.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -51,6 +51,11 @@ def _digest(paths) -> str:
     return h.hexdigest()
 
 
+def _headers() -> list[str]:
+    return [os.path.join(CSRC, h) for h in sorted(os.listdir(CSRC)) if h.endswith(".cuh")] + \
+           [os.path.join(INCLUDE, "b200_abi.h")]
+
+
 def sources() -> list[str]:
     return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
@@ -59,7 +64,7 @@ def is_fresh() -> bool:
     stamp = os.path.join(OBJ_DIR, "stamp")
     if not (os.path.exists(LIB_PATH) and os.path.exists(stamp)):
         return False
-    deps = sources() + [os.path.join(CSRC, "common.cuh"), os.path.join(INCLUDE, "b200_abi.h")]
+    deps = sources() + _headers()
     with open(stamp) as f:
         return f.read().strip() == _digest(deps)
 
@@ -91,7 +96,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(INCLUDE, "b200_abi.h")]
+    deps = srcs + _headers()
     with open(os.path.join(OBJ_DIR, "stamp"), "w") as f:
         f.write(_digest(deps))
     return LIB_PATH

@@ -24,7 +24,11 @@ the hot path this repo owns:
     (``b200ops.comm.PeerComm``); ``B200_FUSED_ALLREDUCE=0`` keeps NCCL for the reduction.  The
     arithmetic (rounding points included) is the reference sequence's.
 
-GEMMs stay ``torch.matmul(..., out=)`` (cuBLAS; out of scope).
+  * the four GEMMs of a decode layer (and ``lm_head``) run, for batches of up to 128 rows, on the
+    tcgen05 weight-streaming kernel ``b200_stream_gemm`` over nn.Linear-layout
+    (``[out, in]``) per-rank weight slices, with the QKV bias add (:145-147) and the SwiGLU launch
+    (:183-184) folded into the epilogues; ``B200_STREAM_GEMM=0`` keeps ``torch.matmul`` (cuBLAS) on the
+    reference's ``[in, out]`` weights plus the separate elementwise launches.
 """
 import logging
 import os
@@ -77,6 +81,12 @@ class ModelGraphRunner:
         # launches N/64 CTAs without split-K and reaches 0.5 of the HBM roofline (36.7 us vs 25.7 us for
         # [32, 14336] x [14336, 4096]); "1" forces it for every shape it supports, "0" keeps torch.matmul everywhere.
         self._skinny = os.environ.get("B200_SKINNY_GEMM", "auto")
+        # B200_STREAM_GEMM = "auto" (default): the tcgen05 weight-streaming kernel runs every decode GEMM of <= 128 rows
+        # whose shape it accepts, with the bias / SwiGLU epilogues fused; "0": cuBLAS + separate launches.
+        # B200_STREAM_GEMM_PDL = 1 launches them with programmatic dependent launch (weight boxes requested before the
+        # previous kernel has drained).
+        self._stream = os.environ.get("B200_STREAM_GEMM", "auto") != "0" and torch.device(device).type == "cuda"
+        self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "0") == "1"
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
         self.rope = RoPE()
@@ -113,6 +123,15 @@ class ModelGraphRunner:
             if bias is not None:
                 b_q, b_k, b_v = bias.split([q_dim, kv_dim, kv_dim], dim=0)
                 block.attn._qkv_b = torch.cat([b.chunk(ws, dim=0)[r] for b in (b_q, b_k, b_v)], dim=0)
+            if self._stream:
+                # nn.Linear layout ([out, in], K contiguous) per-rank slices for b200_stream_gemm; at TP = 1 the q/k/v, o and
+                # down matrices are the model's own tensors (no copy); gate_up is interleaved row-wise (up_j, gate_j)
+                # (`.data`: plain tensors that keep the storage alive even if a caller later rebinds the Parameter)
+                block.attn._qkv_nk = (block.attn.c_attn.weight.data if ws == 1 else
+                                      torch.cat([w.chunk(ws, dim=0)[r] for w in (w_q, w_k, w_v)], dim=0).contiguous())
+                block.attn._o_nk = block.attn.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
+                block.mlp._d_nk = block.mlp.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
+                block.mlp._gu_nk = b200ops.interleave_up_gate(w1.chunk(ws, dim=0)[r], w2.chunk(ws, dim=0)[r])
 
     def _alloc_bufs(self):
         mb, dev, dt = self.max_bs, self.device, self.dtype
@@ -171,8 +190,15 @@ class ModelGraphRunner:
             out.add_(bias)
         return out
 
+    def _use_stream(self, m, w_nk):
+        return self._stream and w_nk is not None and b200ops.stream_gemm_ok(m, w_nk.shape[1], w_nk.shape[0])
+
     def _qkv_proj(self, block, bs):
         """QKV projection of ``self._normed[:bs]`` (the ln_1 norm was fused into the previous launch)."""
+        w_nk = getattr(block.attn, "_qkv_nk", None)
+        if self._use_stream(bs, w_nk):
+            return b200ops.stream_gemm(self._normed[:bs], w_nk, out=self._qkv[:bs], bias=block.attn._qkv_b,
+                                       pdl=self._stream_pdl)
         return self._mm(self._normed[:bs], block.attn._qkv_w, self._qkv[:bs], block.attn._qkv_b)
 
     def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced=False):
@@ -190,12 +216,31 @@ class ModelGraphRunner:
                                   cache_lens, block_table, softmax_scale=self.attention.scale,
                                   rotary_interleaved=False, out=attn, pdl=0 if balanced else self.use_pdl,
                                   balanced=balanced)
+        w_nk = getattr(block.attn, "_o_nk", None)
+        if self._use_stream(bs, w_nk):
+            return b200ops.stream_gemm(self._attn[:bs], w_nk, out=self._attn_out[:bs], pdl=self._stream_pdl)
         return self._mm(self._attn[:bs], block.attn._o, self._attn_out[:bs])
 
     def _ffn(self, x_normed, block, bs, fast_mode=False):
-        self._mm(x_normed, block.mlp._gu, self._gate_up[:bs])
-        swiglu_gemm(self._gate_up[:bs], self._swiglu_out[:bs])
+        gu_nk, d_nk = getattr(block.mlp, "_gu_nk", None), getattr(block.mlp, "_d_nk", None)
+        if self._use_stream(bs, gu_nk) and gu_nk.shape[0] % 16 == 0:
+            # gate_up projection + SwiGLU in one launch (reference :183-184)
+            b200ops.stream_gemm(x_normed, gu_nk, out=self._swiglu_out[:bs], swiglu=True, pdl=self._stream_pdl)
+        else:
+            self._mm(x_normed, block.mlp._gu, self._gate_up[:bs])
+            swiglu_gemm(self._gate_up[:bs], self._swiglu_out[:bs])
+        if self._use_stream(bs, d_nk):
+            return b200ops.stream_gemm(self._swiglu_out[:bs], d_nk, out=self._mlp_out[:bs], pdl=self._stream_pdl)
         return self._mm(self._swiglu_out[:bs], block.mlp._d, self._mlp_out[:bs])
+
+    def _lm_head(self, x):
+        """``lm_head`` (reference :223): the weight is already in the nn.Linear layout the stream GEMM takes."""
+        head = self.model.lm_head
+        w = getattr(head, "weight", None)
+        if (isinstance(head, torch.nn.Linear) and head.bias is None and w is not None and w.dtype == torch.bfloat16
+                and w.is_contiguous() and self._use_stream(x.shape[0], w) and os.environ.get("B200_STREAM_LM_HEAD", "1") != "0"):
+            return b200ops.stream_gemm(x, w, out=self._logits[:x.shape[0]], pdl=self._stream_pdl)
+        return head(x)
 
     # ------------------------------------------------------------------ decode step
     def _reduce_add_norm(self, slot, x, residual, norm, y, res_out, ss_rounded):
@@ -233,7 +278,7 @@ class ModelGraphRunner:
             nxt = (ln_f if fuse_ln_f else None) if last else tr.h[layer_idx + 1].ln_1
             self._reduce_add_norm(1, mlp_out, residual, nxt, normed, h_buf, ss_rounded=True)
             h = h_buf
-        return self.model.lm_head(normed if fuse_ln_f else ln_f(h))
+        return self._lm_head(normed if fuse_ln_f else ln_f(h))
 
     # A batch whose longest sequence exceeds this multiple of the mean length is "ragged": the split-KV grid
     # (one launch-constant split count for every row) leaves most SMs idle behind the long rows, the balanced
@@ -261,8 +306,9 @@ class ModelGraphRunner:
                 torch.cuda.synchronize()
                 g = torch.cuda.CUDAGraph()
                 with torch.no_grad(), torch.cuda.graph(g):
-                    self._logits[:bs] = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True,
-                                                    balanced=balanced)
+                    lg = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True, balanced=balanced)
+                    if lg.data_ptr() != self._logits.data_ptr():     # lm_head through cuBLAS allocates its own output
+                        self._logits[:bs] = lg
                     if greedy:
                         b200ops.greedy_argmax(self._logits[:bs], self._next_ids[:bs])
                 if balanced:
@@ -278,7 +324,9 @@ class ModelGraphRunner:
 
     def gemm_policy(self) -> str:
         """Which kernels run the four decode GEMMs (reported by the bench tools)."""
-        return f"B200_SKINNY_GEMM={self._skinny}"
+        if self._stream:
+            return "tcgen05 stream_gemm (bias / SwiGLU epilogues fused)" + (" + PDL" if self._stream_pdl else "")
+        return f"cuBLAS (torch.matmul), B200_SKINNY_GEMM={self._skinny}"
 
     def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
         if self._comm is not None:

@@ -55,23 +55,25 @@ def to_dev(case, dev="cuda"):
 # so the size of the tolerance tail that the CUDA kernels actually use is on file.
 PARITY_LOG = []
 
-# Tail allowance, pinned to what was MEASURED on the B200 over the whole GPU suite
-# (profiles/r02/parity_tail.json): see the docstring of assert_close.
-TAIL_FRAC = 3e-4
-TAIL_SCALE = 5.0
+# Tail allowance, pinned to what was MEASURED on the B200 over the whole GPU suite (profiles/r02/parity_tail.json,
+# 291 assert_close calls of the round-2 suite): 256 calls have NO element outside the north_star bound; the other
+# 35 have 1-4 elements outside it (at most 2.4e-4 of a tensor), the worst at 1.64 x the bound (9.8e-3 absolute).
+# The allowance is that measurement + 1 element and x 1.5: at most TAIL_ELEMS elements, each inside TAIL_SCALE x bound.
+TAIL_ELEMS = 5
+TAIL_SCALE = 2.5
 
 
-def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_frac=None, tail_scale=None):
+def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_elems=None, tail_scale=None):
     """north_star tolerance against the fp32 oracle: |a - e| <= 2e-3 + 1e-2 * |e|.
 
     Attention probabilities enter the P.V tensor-core product as bf16 (8-bit mantissa) — in this
     kernel exactly as in flash-attn — so an output that is a near-cancelling sum of O(1) terms
     can miss the bound by a few 1e-3.  The bar is: every element inside the bound, except a tail
-    of at most max(2, TAIL_FRAC * numel) elements which must still be inside TAIL_SCALE x the
-    bound; anything systematic (a wrong page, a wrong rotation, a missed token) produces
+    of at most TAIL_ELEMS elements (an absolute count, whatever the tensor size) which must still
+    be inside TAIL_SCALE x the bound; anything systematic (a wrong page, a wrong rotation, a missed token) produces
     O(0.1 - 1) errors on many elements and fails both clauses.  Returns (n_out_of_bound,
     worst err / bound) and logs them (PARITY_LOG)."""
-    tail_frac = TAIL_FRAC if tail_frac is None else tail_frac
+    allowed = TAIL_ELEMS if tail_elems is None else tail_elems
     tail_scale = TAIL_SCALE if tail_scale is None else tail_scale
     a = actual.float().cpu()
     e = expected_f32.float().cpu()
@@ -80,7 +82,6 @@ def assert_close(actual, expected_f32, atol=2e-3, rtol=1e-2, what="out", tail_fr
     lim = atol + rtol * e.abs()
     bad = err > lim
     n_bad = int(bad.sum())
-    allowed = max(2, int(tail_frac * bad.numel()))
     worst = float((err / lim).max()) if bad.numel() else 0.0
     import os
     PARITY_LOG.append({"test": os.environ.get("PYTEST_CURRENT_TEST", "").split(" ")[0], "what": what,

@@ -26,8 +26,8 @@ CASES = {
     # round 2: BASELINE.json configs[1] at full size, one 128k-context row (configs[4]), D = 64 and G = 7 prefill
     "decode_llama8b_b32_4k_cfg2": (dict(B=32, Hq=32, Hkv=8, D=128, lens=[4095] * 32, seed=7), False, True),
     "decode_llama8b_b1_128k": (dict(B=1, Hq=32, Hkv=8, D=128, lens=[131071], seed=8, rot_rows=131080), False, True),
-    "prefill_gqa7_d64": (dict(B=1, Hq=14, Hkv=2, D=64, lens=[0], S_new=300, seed=9), False, True),
-    "prefill_gqa7_d128_prefix": (dict(B=2, Hq=28, Hkv=4, D=128, lens=[100, 300], S_new=200, seed=10), False, True),
+    "prefill_gqa7_d64": (dict(B=1, Hq=7, Hkv=1, D=64, lens=[0], S_new=300, seed=9), False, True),
+    "prefill_gqa7_d128_prefix": (dict(B=1, Hq=7, Hkv=1, D=128, lens=[300], S_new=200, seed=10), False, True),
     "prefill_empty_d128": (dict(B=1, Hq=8, Hkv=2, D=128, lens=[0], S_new=150, seed=4), False, False),
     "prefill_prefix_d128": (dict(B=1, Hq=4, Hkv=1, D=128, lens=[200], S_new=130, seed=5), False, True),
 }
