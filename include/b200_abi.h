@@ -147,6 +147,8 @@ int b200_greedy_argmax(const void* logits, int logits_dtype,
 #define B200_GEMM_EPI_SWIGLU 2
 #define B200_GEMM_FLAG_PDL   1
 int64_t b200_stream_gemm_workspace_bytes(int M, int64_t N, int grid_hint);
+/* debug only: uint64 [grid][8] device buffer the next launches stamp with %globaltimer per CTA (NULL = off) */
+void b200_debug_stream_gemm_trace(void* dev_ptr);
 int b200_stream_gemm(const void* x, const void* w, const void* bias, void* out,
                      void* workspace, int64_t workspace_bytes,
                      int M, int64_t K, int64_t N, int64_t ldx, int64_t ldw, int64_t ldo,

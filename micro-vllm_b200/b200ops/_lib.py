@@ -104,6 +104,7 @@ SIGNATURES = {
     "b200_greedy_argmax_workspace_bytes": (_i64, [_i64]),
     "b200_greedy_argmax": (C.c_int, [_vp, C.c_int, _i64, _i64, _i64, _vp, _vp, _i64, _vp]),
     "b200_stream_gemm_workspace_bytes": (_i64, [C.c_int, _i64, C.c_int]),
+    "b200_debug_stream_gemm_trace": (None, [_vp]),
     "b200_stream_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_int, _i64, _i64, _i64, _i64, _i64,
                                     C.c_int, C.c_int, C.c_int, _vp]),
     "b200_skinny_gemm_splits": (C.c_int, [C.c_int, _i64, _i64, C.c_int]),

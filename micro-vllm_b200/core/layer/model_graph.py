@@ -81,11 +81,14 @@ class ModelGraphRunner:
         # launches N/64 CTAs without split-K and reaches 0.5 of the HBM roofline (36.7 us vs 25.7 us for
         # [32, 14336] x [14336, 4096]); "1" forces it for every shape it supports, "0" keeps torch.matmul everywhere.
         self._skinny = os.environ.get("B200_SKINNY_GEMM", "auto")
-        # B200_STREAM_GEMM = "auto" (default): the tcgen05 weight-streaming kernel runs every decode GEMM of <= 128 rows
-        # whose shape it accepts, with the bias / SwiGLU epilogues fused; "0": cuBLAS + separate launches.
-        # B200_STREAM_GEMM_PDL = 1 launches them with programmatic dependent launch (weight boxes requested before the
-        # previous kernel has drained).
-        self._stream = os.environ.get("B200_STREAM_GEMM", "auto") != "0" and torch.device(device).type == "cuda"
+        # B200_STREAM_GEMM: "auto" (default) sends a decode GEMM of <= 128 rows through the tcgen05 weight-streaming
+        # kernel where it was measured faster than cuBLAS on B200 (profiles/r02/stream_gemm_*.json): deep-K, narrow-N
+        # products (K >= 4 N: the QKV projection of a TP shard, where cuBLAS has too few tiles and no split-K and sits at
+        # 0.26 of the HBM roofline); "1" uses it for every shape it accepts, with the bias / SwiGLU epilogues fused;
+        # "0": cuBLAS + separate launches everywhere.  B200_STREAM_GEMM_PDL = 1 launches them with programmatic
+        # dependent launch (weight boxes requested before the previous kernel has drained).
+        self._stream_mode = os.environ.get("B200_STREAM_GEMM", "auto")
+        self._stream = self._stream_mode != "0" and torch.device(device).type == "cuda"
         self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "0") == "1"
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
@@ -191,7 +194,9 @@ class ModelGraphRunner:
         return out
 
     def _use_stream(self, m, w_nk):
-        return self._stream and w_nk is not None and b200ops.stream_gemm_ok(m, w_nk.shape[1], w_nk.shape[0])
+        if not (self._stream and w_nk is not None and b200ops.stream_gemm_ok(m, w_nk.shape[1], w_nk.shape[0])):
+            return False
+        return self._stream_mode == "1" or w_nk.shape[1] >= 4 * w_nk.shape[0]
 
     def _qkv_proj(self, block, bs):
         """QKV projection of ``self._normed[:bs]`` (the ln_1 norm was fused into the previous launch)."""
@@ -325,7 +330,8 @@ class ModelGraphRunner:
     def gemm_policy(self) -> str:
         """Which kernels run the four decode GEMMs (reported by the bench tools)."""
         if self._stream:
-            return "tcgen05 stream_gemm (bias / SwiGLU epilogues fused)" + (" + PDL" if self._stream_pdl else "")
+            which = "every decode GEMM" if self._stream_mode == "1" else "K >= 4N products (QKV of a TP shard), cuBLAS elsewhere"
+            return f"tcgen05 stream_gemm for {which}" + (" + PDL" if self._stream_pdl else "")
         return f"cuBLAS (torch.matmul), B200_SKINNY_GEMM={self._skinny}"
 
     def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:

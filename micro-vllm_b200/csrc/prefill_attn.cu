@@ -89,6 +89,22 @@ __device__ __forceinline__ float softmax_exp_tile(const uint32_t (&su)[TOTAL], f
     return a + b;
 }
 
+// Zero the V rows of tokens >= `valid` in a [128 tokens][D] shared-memory tile (DSLABS slabs of [128][64] bf16, one
+// 128-byte swizzle row per token: zeroing whole rows is swizzle-invariant).  A masked token's probability is exactly
+// 0, but the TMA box brings in whatever bytes sit in never-written cache slots, and 0 * NaN / Inf would poison every
+// output row of the tile (flash-attn clears out-of-bounds V; the decode kernel zero-fills these rows).
+template <int DSLABS>
+__device__ __forceinline__ void zero_v_tail(uint32_t v_tile, int valid, int lane, int nlanes) {
+    const int n = (128 - valid) * DSLABS * 8;
+    for (int i = lane; i < n; i += nlanes) {
+        const int chunk = i & 7, t = i >> 3;
+        const int sl = t % DSLABS, row = valid + t / DSLABS;
+        asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};"
+                     :: "r"(v_tile + (uint32_t)(sl * (128 * 128) + row * 128 + chunk * 16)), "r"(0u) : "memory");
+    }
+    fence_async_smem();                 // generic-proxy writes -> visible to the tensor core's async proxy
+}
+
 // ------------------------------------------------------------------ kernel 1: RoPE + append
 struct AppendParams {
     const __nv_bfloat16* q; const __nv_bfloat16* k; const __nv_bfloat16* v;
@@ -265,6 +281,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
             auto issue_pv = [&](int t) {
                 const int st = t & 1;
                 mbar_wait(bar(BAR_VF + st), (uint32_t)(t >> 1) & 1u);
+                if (t == n_tiles - 1 && seqlen_k - t * C::BN < C::BN)
+                    zero_v_tail<C::DSLABS>(sV + st * C::TILE_B, seqlen_k - t * C::BN, 0, 1);
                 mbar_wait(bar(BAR_PF), (uint32_t)t & 1u);
                 tc_fence_after();
 #pragma unroll
@@ -551,6 +569,10 @@ prefill_attn_tmem_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_
             const int st = t % C::KV_STAGES;
             pf_stamp(p, lane == 0, 7, t);
             mbar_wait(bar(B2_VF + st), (uint32_t)(t / C::KV_STAGES) & 1u);
+            if (t == n_tiles - 1 && seqlen_k - t * C::BN < C::BN) {
+                zero_v_tail<C::DSLABS>(sV + st * C::TILE_B, seqlen_k - t * C::BN, lane, 32);
+                __syncwarp();
+            }
             mbar_wait(bar(B2_PF), (uint32_t)t & 1u);
             pf_stamp(p, lane == 0, 8, t);
             tc_fence_after();
@@ -952,6 +974,10 @@ prefill_attn_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         for (int j = 0; j < n_tiles; ++j) {
             const bool more = (j + 1 < n_tiles);
             mbar_wait(bar(B3_VF + (j & 1)), (uint32_t)(j >> 1) & 1u);
+            if (!more && seqlen_k - j * C::BN < C::BN) {
+                zero_v_tail<C::DSLABS>(sV + (j & 1) * C::TILE_B, seqlen_k - j * C::BN, lane, 32);
+                __syncwarp();
+            }
             if (more) mbar_wait(bar(B3_KF + ((j + 1) & 1)), (uint32_t)((j + 1) >> 1) & 1u);
             issue_pv(0, j);
             if (more) issue_qk(0, j + 1);

@@ -71,13 +71,24 @@ struct SgParams {
     const __nv_bfloat16* bias;       // [N] or null
     __nv_bfloat16* out;              // [M, N] (EPI_SWIGLU: [M, N / 2])
     float* ws_part;                  // [2 * grid] partial tiles, each [NB][128] fp32
-    uint32_t* ws_cnt;                // [2 * n_tiles]: arrival counters, then done counters (zero between launches)
+    uint32_t* ws_cnt;                // [n_tiles]: arrival / departure counters, wrap to 0 after 2 S increments (zero between launches)
     int M, N, K;
     int64_t ldo;
     int n_tiles, kblocks;            // 128-row weight tiles, 64-element k-blocks
     long long units;                 // n_tiles * kblocks
     int epilogue, flags;
+    unsigned long long* trace;       // debug only (b200_debug_stream_gemm_trace): [grid][8] %globaltimer stamps
 };
+
+// Timeline of every CTA (debug): 0 entry, 1 setup done, 2 all loads issued, 3 first stage landed, 4 last MMA committed,
+// 5 last accumulator drained, 6 peers' partials complete (first shared tile), 7 exit
+__device__ __forceinline__ void sg_stamp(const SgParams& p, int ev) {
+    if (p.trace != nullptr) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(size_t)blockIdx.x * 8 + ev] = t;
+    }
+}
 
 template <int NB_>
 struct SgCfg {
@@ -128,6 +139,7 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     const bool pdl = (p.flags & B200_GEMM_FLAG_PDL) != 0;
 
     if (tid == 0) {
+        sg_stamp(p, 0);
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(accf_bar(b), 1); mbar_init(acce_bar(b), 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -144,6 +156,7 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     const uint32_t tmem = *s_tmem;
     // the kernel after this one may start its own prologue now (its griddepcontrol.wait still waits for ALL of this grid)
     if (pdl) griddep_launch();
+    if (tid == 0) sg_stamp(p, 1);
 
     if (warp == 0) {
         // ===================================================== TMA producer
@@ -151,32 +164,39 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
             uint64_t pol_w, pol_x;
             asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));   // weights: read once
             asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_x));    // activations: re-read by every CTA
-            const long long n_units = u_end - u_begin;
-            // ring fill: the weight boxes go out before the dependency on the previous kernel resolves
-            const int pre = (int)(n_units < STAGES ? n_units : STAGES);
-            for (int i = 0; i < pre; ++i) {
-                const long long u = u_begin + i;
-                const int tile = (int)(u / KB), kb = (int)(u - (long long)tile * KB);
-                mbar_expect_tx(full_bar(i), C::STAGE_BYTES);
-                tma_load_2d_hint(base + i * C::STAGE_BYTES, &tm_w, full_bar(i), kb * 64, tile * 128, pol_w);
+            const int n_units = (int)(u_end - u_begin);
+            int tile = (int)(u_begin / KB), kb = (int)(u_begin - (long long)tile * KB);        // the only division
+            int i = 0;
+            if (pdl) {
+                // ring fill: the weight boxes go out before the dependency on the previous kernel resolves ...
+                const int pre = n_units < STAGES ? n_units : STAGES;
+                int t2 = tile, k2 = kb;
+                for (int j = 0; j < pre; ++j) {
+                    mbar_expect_tx(full_bar(j), C::STAGE_BYTES);
+                    tma_load_2d_hint(base + j * C::STAGE_BYTES, &tm_w, full_bar(j), k2 * 64, t2 * 128, pol_w);
+                    if (++k2 == KB) { k2 = 0; ++t2; }
+                }
+                griddep_wait();                                   // ... x (and the workspace) are only touched below this line
+                for (int j = 0; j < pre; ++j) {
+                    tma_load_2d_hint(base + j * C::STAGE_BYTES + C::A_BYTES, &tm_x, full_bar(j), kb * 64, 0, pol_x);
+                    if (++kb == KB) { kb = 0; ++tile; }
+                }
+                i = pre;
             }
-            if (pdl) griddep_wait();                              // x (and the workspace) are only touched below this line
-            for (int i = 0; i < pre; ++i) {
-                const long long u = u_begin + i;
-                const int kb = (int)(u % KB);
-                tma_load_2d_hint(base + i * C::STAGE_BYTES + C::A_BYTES, &tm_x, full_bar(i), kb * 64, 0, pol_x);
-            }
-            int stage = pre % STAGES;
-            uint32_t phase = (pre == STAGES) ? 1u : 0u;           // parity of the NEXT wait on empty_bar(stage)
-            for (long long u = u_begin + pre; u < u_end; ++u) {
-                const int tile = (int)(u / KB), kb = (int)(u - (long long)tile * KB);
-                mbar_wait(empty_bar(stage), phase ^ 1u);
+            int stage = i % STAGES;
+            uint32_t phase = (i >= STAGES) ? 1u : 0u;             // parity of the NEXT completion of empty_bar(stage) to wait for, flipped
+            for (; i < n_units; ++i) {
+                if (i >= STAGES) mbar_wait(empty_bar(stage), phase ^ 1u);
+                const uint32_t dst = base + stage * C::STAGE_BYTES;
                 mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
-                tma_load_2d_hint(base + stage * C::STAGE_BYTES, &tm_w, full_bar(stage), kb * 64, tile * 128, pol_w);
-                tma_load_2d_hint(base + stage * C::STAGE_BYTES + C::A_BYTES, &tm_x, full_bar(stage), kb * 64, 0, pol_x);
+                tma_load_2d_hint(dst, &tm_w, full_bar(stage), kb * 64, tile * 128, pol_w);
+                tma_load_2d_hint(dst + C::A_BYTES, &tm_x, full_bar(stage), kb * 64, 0, pol_x);
+                if (++kb == KB) { kb = 0; ++tile; }
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
+            sg_stamp(p, 2);
         }
+        __syncwarp();                                             // the idle lanes must not run ahead into the final CTA barrier
     } else if (warp == 1) {
         // ===================================================== MMA issuer (whole warp loops, one elected lane issues)
         constexpr uint32_t IDESC = umma_idesc_bf16(128, NB, 0, 0);    // A = weights K-major, B = activations K-major
@@ -196,6 +216,7 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
             for (; u < seg_end; ++u) {
                 mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
+                if (u == u_begin && lane == 0) sg_stamp(p, 3);
                 if (elect_one()) {
                     const uint32_t a_base = base + stage * C::STAGE_BYTES;
                     const uint32_t b_base = a_base + C::A_BYTES;
@@ -213,6 +234,7 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
             }
             if (elect_one()) tc_commit(accf_bar(buf));             // segment accumulated
             __syncwarp();
+            if (u >= u_end && lane == 0) sg_stamp(p, 4);
             acc_phase[buf] ^= 1u;
             buf ^= 1;
         }
@@ -223,6 +245,7 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
         const int et = (warp - 2) * 32 + lane;                     // 0 .. 127
         const int row_in_tile = quarter * 32 + lane;               // TMEM lane = output feature within the tile
         const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        constexpr int CW = NB < 64 ? NB : 64;                      // accumulator columns held in registers at a time
         int buf = 0;
         uint32_t acc_phase[2] = {0u, 0u};
         // up to two tiles of this CTA end up as partials that need the distributed reduction
@@ -233,69 +256,67 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
             const long long tile_beg = (long long)tile * KB, tile_end = tile_beg + KB;
             const long long seg_end = tile_end < u_end ? tile_end : u_end;
             const bool whole = (u == tile_beg) && (seg_end == tile_end);
+            const bool starts = (u == tile_beg);
             mbar_wait(accf_bar(buf), acc_phase[buf]);
             tc_fence_after();
             const uint32_t t_addr = tmem + lane_sel + (uint32_t)(buf * NB);
             const int n = tile * 128 + row_in_tile;
-            if (whole) {
-                // ---- this CTA owns the whole K range of the tile: finish it from TMEM
-                float bias_v = 0.0f;
-                if (p.epilogue == EPI_BIAS && n < p.N) bias_v = __bfloat162float(p.bias[n]);
+            float bias_v = 0.0f;
+            if (whole && p.epilogue == EPI_BIAS && n < p.N) bias_v = __bfloat162float(p.bias[n]);
+            // partial: fp32 tile [NB][128] into this CTA's slot (slot 1 = the segment that STARTS a tile)
+            float* dst = p.ws_part + (size_t)(2 * (int)c + (starts ? 1 : 0)) * (NB * 128) + row_in_tile;
 #pragma unroll
-                for (int c0 = 0; c0 < NB; c0 += 16) {
-                    uint32_t r[16];
-                    tmem_ld16(t_addr + c0, r);
-                    tmem_wait_ld();
-                    if (p.epilogue == EPI_SWIGLU) {
-                        // lanes 2i / 2i+1 hold up_i / gate_i of output column tile * 64 + i
+            for (int c0 = 0; c0 < NB; c0 += CW) {
+                uint32_t r[CW];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float mine = bf16_round(__uint_as_float(r[i]));
-                            const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
-                            const int m = c0 + i;
-                            if (!(lane & 1) && m < p.M && n < p.N)
-                                p.out[(int64_t)m * p.ldo + (n >> 1)] = __float2bfloat16_rn(silu_mul(other, mine));
-                        }
-                    } else {
+                for (int q = 0; q < CW; q += 16) tmem_ld16(t_addr + c0 + q, *reinterpret_cast<uint32_t(*)[16]>(&r[q]));
+                tmem_wait_ld();
+                if (c0 + CW >= NB) {                               // everything is in registers: hand the accumulator back
+                    tc_fence_before();
+                    mbar_arrive(acce_bar(buf));
+                }
+                if (!whole) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const int m = c0 + i;
-                            float v = __uint_as_float(r[i]);
-                            if (p.epilogue == EPI_BIAS) v = bf16_round(v) + bias_v;
-                            if (m < p.M && n < p.N) p.out[(int64_t)m * p.ldo + n] = __float2bfloat16_rn(v);
-                        }
+                    for (int i = 0; i < CW; ++i) dst[(c0 + i) * 128] = __uint_as_float(r[i]);
+                } else if (p.epilogue == EPI_SWIGLU) {
+                    // lanes 2i / 2i+1 hold up_i / gate_i of output column tile * 64 + i
+#pragma unroll
+                    for (int i = 0; i < CW; ++i) {
+                        const float mine = bf16_round(__uint_as_float(r[i]));
+                        const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
+                        const int m = c0 + i;
+                        if (!(lane & 1) && m < p.M && n < p.N)
+                            p.out[(int64_t)m * p.ldo + (n >> 1)] = __float2bfloat16_rn(silu_mul(other, mine));
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < CW; ++i) {
+                        const int m = c0 + i;
+                        float v = __uint_as_float(r[i]);
+                        if (p.epilogue == EPI_BIAS) v = bf16_round(v) + bias_v;
+                        if (m < p.M && n < p.N) p.out[(int64_t)m * p.ldo + n] = __float2bfloat16_rn(v);
                     }
                 }
-            } else {
-                // ---- partial: fp32 tile [NB][128] into this CTA's slot (slot 1 = the segment that STARTS a tile)
-                const int slot = 2 * (int)c + ((u == tile_beg) ? 1 : 0);
-                float* dst = p.ws_part + (size_t)slot * (NB * 128) + row_in_tile;
-#pragma unroll
-                for (int c0 = 0; c0 < NB; c0 += 16) {
-                    uint32_t r[16];
-                    tmem_ld16(t_addr + c0, r);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) dst[(c0 + i) * 128] = __uint_as_float(r[i]);
-                }
-                duty_tile[(u == tile_beg) ? 1 : 0] = tile;
             }
-            tc_fence_before();
-            mbar_arrive(acce_bar(buf));                            // accumulator may be overwritten
             if (!whole) {
-                // publish the partial: all 128 epilogue threads have stored, then ONE release-arrive on the tile counter
+                duty_tile[starts ? 1 : 0] = tile;
+                // publish the partial: all 128 epilogue threads have stored, then ONE release-increment of the tile's
+                // counter (fire and forget: nobody waits for the atomic's round trip).  The counter wraps to 0 after 2 S
+                // increments (S arrivals + S departures), so it is re-armed for the next launch without a reset.
                 asm volatile("bar.sync 1, 128;" ::: "memory");
                 if (et == 0) {
-                    __threadfence();
-                    atomicAdd(p.ws_cnt + tile, 1u);
+                    const int S = sg_owner(tile_beg + KB - 1, U, G) - sg_owner(tile_beg, U, G) + 1;
+                    asm volatile("red.release.gpu.global.inc.u32 [%0], %1;" :: "l"(p.ws_cnt + tile), "r"((uint32_t)(2 * S - 1)) : "memory");
                 }
             }
             acc_phase[buf] ^= 1u;
             buf ^= 1;
             u = seg_end;
         }
+        if (et == 0) sg_stamp(p, 5);
+        bool stamped = false;
         // ---- distributed reduction of the shared tiles: every CTA of a tile's group reduces an equal slice of
-        // the batch rows over ALL partials in CTA order, applies the epilogue, and the last one re-arms the counters
+        // the batch rows over ALL partials in CTA order (deterministic) and applies the epilogue
 #pragma unroll 1
         for (int d = 0; d < 2; ++d) {
             const int tile = duty_tile[d];
@@ -309,52 +330,74 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
                     if (++spins > (1u << 28)) __trap();             // protocol bug: fail loudly, never hang
                 }
             }
+            if (et == 0 && !stamped) { sg_stamp(p, 6); stamped = true; }
             asm volatile("bar.sync 1, 128;" ::: "memory");
             const int m_lo = (int)((long long)p.M * s_me / S), m_hi = (int)((long long)p.M * (s_me + 1) / S);
             const int n4 = (et & 31) * 4;                          // 4 consecutive features of the tile
             const int n = tile * 128 + n4;
-            for (int m = m_lo + (et >> 5); m < m_hi; m += 4) {
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int s = 0; s < S; ++s) {
-                    const int cc = c_first + s;
-                    const int slot = 2 * cc + (s == 0 ? 1 : 0);
-                    const float4 v = ld_cg_f4(p.ws_part + (size_t)slot * (NB * 128) + m * 128 + n4);
-                    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            // Two batch rows per pass and up to 8 partials per row are requested before the first add (16 independent
+            // L2 round trips in flight per thread); the adds run in fixed CTA order, zeros stand in for absent partials.
+            const float* part0 = p.ws_part + (size_t)(2 * c_first + 1) * (NB * 128) + n4;     // CTA c_first: slot 2c+1
+            const float* partk = p.ws_part + (size_t)(2 * (c_first + 1)) * (NB * 128) + n4;   // CTA c_first+s: slot 2c
+            for (int m = m_lo + (et >> 5); m < m_hi; m += 8) {
+                const bool two = (m + 4) < m_hi;
+                float4 acc[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+                for (int s0 = 0; s0 < S; s0 += 8) {
+                    float4 v[2][8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int s2 = s0 + j;
+                        const float* src = (s2 == 0) ? part0 : partk + (size_t)(s2 - 1) * (2 * NB * 128);
+                        v[0][j] = (s2 < S) ? ld_cg_f4(src + m * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        v[1][j] = (s2 < S && two) ? ld_cg_f4(src + (m + 4) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            acc[h].x += v[h][j].x; acc[h].y += v[h][j].y; acc[h].z += v[h][j].z; acc[h].w += v[h][j].w;
+                        }
+                    }
                 }
                 if (n >= p.N) continue;
-                if (p.epilogue == EPI_SWIGLU) {
-                    const float u0 = bf16_round(acc.x), g0 = bf16_round(acc.y), u1 = bf16_round(acc.z), g1 = bf16_round(acc.w);
-                    *reinterpret_cast<uint32_t*>(p.out + (int64_t)m * p.ldo + (n >> 1)) =
-                        pack_bf16(silu_mul(g0, u0), silu_mul(g1, u1));
-                } else {
-                    float v[4] = {acc.x, acc.y, acc.z, acc.w};
-                    if (p.epilogue == EPI_BIAS) {
-                        const uint2 bb = *reinterpret_cast<const uint2*>(p.bias + n);
-                        v[0] = bf16_round(v[0]) + bf16lo(bb.x); v[1] = bf16_round(v[1]) + bf16hi(bb.x);
-                        v[2] = bf16_round(v[2]) + bf16lo(bb.y); v[3] = bf16_round(v[3]) + bf16hi(bb.y);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (h == 1 && !two) break;
+                    const int mm = m + 4 * h;
+                    const float4 a4 = acc[h];
+                    if (p.epilogue == EPI_SWIGLU) {
+                        const float u0 = bf16_round(a4.x), g0 = bf16_round(a4.y), u1 = bf16_round(a4.z), g1 = bf16_round(a4.w);
+                        *reinterpret_cast<uint32_t*>(p.out + (int64_t)mm * p.ldo + (n >> 1)) =
+                            pack_bf16(silu_mul(g0, u0), silu_mul(g1, u1));
+                    } else {
+                        float v4[4] = {a4.x, a4.y, a4.z, a4.w};
+                        if (p.epilogue == EPI_BIAS) {
+                            const uint2 bb = *reinterpret_cast<const uint2*>(p.bias + n);
+                            v4[0] = bf16_round(v4[0]) + bf16lo(bb.x); v4[1] = bf16_round(v4[1]) + bf16hi(bb.x);
+                            v4[2] = bf16_round(v4[2]) + bf16lo(bb.y); v4[3] = bf16_round(v4[3]) + bf16hi(bb.y);
+                        }
+                        uint2 o;
+                        o.x = pack_bf16(v4[0], v4[1]); o.y = pack_bf16(v4[2], v4[3]);
+                        *reinterpret_cast<uint2*>(p.out + (int64_t)mm * p.ldo + n) = o;
                     }
-                    uint2 o;
-                    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
-                    *reinterpret_cast<uint2*>(p.out + (int64_t)m * p.ldo + n) = o;
                 }
             }
+            // departure: my reads of the partials are done (the loads above have returned: their values were consumed)
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (et == 0) {
-                const uint32_t done = atomicAdd(p.ws_cnt + p.n_tiles + tile, 1u);
-                if (done == (uint32_t)S - 1) {                      // everybody has read the partials: re-arm for the next launch
-                    p.ws_cnt[tile] = 0u;
-                    p.ws_cnt[p.n_tiles + tile] = 0u;
-                }
-            }
+            if (et == 0)
+                asm volatile("red.relaxed.gpu.global.inc.u32 [%0], %1;" :: "l"(p.ws_cnt + tile), "r"((uint32_t)(2 * S - 1)) : "memory");
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (tid == 0) sg_stamp(p, 7);
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
     }
 }
+
+static unsigned long long* g_sg_trace = nullptr;
 
 typedef CUresult (*SgEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -440,6 +483,9 @@ static int sg_launch(const CUtensorMap& tw, const CUtensorMap& tx, const SgParam
 
 using namespace b200;
 
+// Debug only: uint64 [grid][8] device buffer that the NEXT launches stamp with %globaltimer (NULL = off).
+extern "C" void b200_debug_stream_gemm_trace(void* dev_ptr) { g_sg_trace = (unsigned long long*)dev_ptr; }
+
 extern "C" int64_t b200_stream_gemm_workspace_bytes(int M, int64_t N, int grid_hint) {
     if (M < 1 || M > 128 || N < 1) return 0;
     const int64_t n_tiles = (N + 127) / 128;
@@ -472,6 +518,7 @@ extern "C" int b200_stream_gemm(const void* x, const void* w, const void* bias, 
     p.kblocks = (int)(K / 64);
     p.units = (long long)p.n_tiles * p.kblocks;
     p.epilogue = epilogue; p.flags = flags;
+    p.trace = g_sg_trace;
     const int grid = sg_grid(p.units, grid_hint);
     const int NB = sg_pad_rows(M);
     const int64_t cnt_bytes = ((2 * (int64_t)p.n_tiles * 4 + 255) / 256) * 256;

@@ -364,9 +364,41 @@ def _peer_worker(rank, world, port, q):
             assert torch.equal(ro[lo:hi].cpu(), wres1[lo:hi]) and torch.equal(rs[lo:hi].cpu(), wres2[lo:hi]), f"ll replay {it}"
             assert int(bf16_ulp_diff(yl.cpu(), wy2).max()) <= 1
         del g3
+        # NVLS form (multimem.ld_reduce / multimem.st on the multicast mapping; only where the node has one): contract of
+        # the sharded form; the in-switch fp32 sum is rounded once, so the residual stream may differ from the
+        # rank-order oracle by the last bf16 ulp; every rank gets the SAME y (one computation, multicast store)
+        if comm.has_multicast:
+            g4 = torch.cuda.CUDAGraph()
+            for bs in (rows, 7, 1, rows):                        # row partitions (and grids) change between calls
+                comm.allreduce_residual_rmsnorm(0, bs, n, rs[:bs], wd, yb[:bs], ro[:bs], 1e-5, True, nvls=True)
+            torch.cuda.synchronize()
+            dist.barrier()
+            with torch.cuda.graph(g4):
+                comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yb, ro, 1e-5, True, nvls=True)
+                comm.allreduce_residual_rmsnorm(0, rows, n, ro, wd, yb, rs, 1e-5, False, nvls=True)
+            for it in range(10):
+                parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
+                r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
+                xs[0].copy_(parts0[rank].to(dev))
+                rs.copy_(r.to(dev))
+                torch.cuda.synchronize()
+                dist.barrier()
+                g4.replay()
+                torch.cuda.synchronize()
+                dist.barrier()
+                wy1, wres1 = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, True)
+                wy2, wres2 = allreduce_residual_rmsnorm_oracle(parts0, wres1, w, 1e-5, False)
+                assert int(bf16_ulp_diff(ro[lo:hi].cpu(), wres1[lo:hi]).max()) <= 1, f"nvls replay {it}"
+                assert int(bf16_ulp_diff(rs[lo:hi].cpu(), wres2[lo:hi]).max()) <= 2, f"nvls replay {it}"
+                ys = [torch.empty_like(yb) for _ in range(world)]
+                dist.all_gather(ys, yb.contiguous())
+                assert all(torch.equal(ys[0], t) for t in ys), "every rank must hold the same normalised rows"
+                d = bf16_ulp_diff(yb.cpu(), wy2)
+                assert int(d.max()) <= 4 and float((d <= 1).float().mean()) > 0.99
+            del g4
         assert comm.error_flag() == 0
-        with pytest.raises(AssertionError):                          # same slot twice in a row is refused on the host
-            comm._last_slot = 1
+        with pytest.raises(AssertionError):                          # same slot right after a one-shot call is refused on the host
+            comm._last_slot, comm._last_mode = 1, "oneshot"
             comm.allreduce_residual_rmsnorm(1, rows, n, rdev, None, None, h, 0.0, True)
         dist.barrier()
         del graph                                # NCCL / peer mappings are torn down only after the graphs are gone

@@ -154,3 +154,32 @@ def test_prefill_then_decode_consistency():
     assert torch.equal(d2["v_cache"], pages_v), "prefill(S) + decode must leave the same V pages as prefill(S+1)"
     assert torch.equal(d2["k_cache"], pages_k), "rotated K written by the decode kernel and the prefill kernel must be bit-identical"
     assert_close(last, full[:, S].float(), what="decode vs last prefill row")
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 6])
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
+def test_prefill_poisoned_cache_tail(variant, D, Hq, Hkv):
+    """never-written cache slots may hold NaN / Inf (torch.empty caches, recycled pages).  Keys at or
+    beyond seqlen_k are masked (P = 0), but the TMA box still brings their V rows into the tile, and 0 * NaN would
+    poison every output row of the tile.  The kernel must zero those rows (flash-attn clears out-of-bounds V; the
+    decode kernel zero-fills them): outputs of a NaN-filled pool must equal the oracle's, which never gathers them."""
+    case = make_paged_case(2, Hq, Hkv, D, [0, 300], S_new=390, seed=61)
+    case["k_cache"].fill_(float("nan"))
+    case["v_cache"].fill_(float("nan"))
+    # the cached prefix of row 1 (300 tokens) must be finite: that IS attended
+    page = case["page"]
+    g = torch.Generator().manual_seed(62)
+    for t in range(300):
+        blk, off = int(case["table"][1, t // page]), t % page
+        case["k_cache"][blk, off] = torch.randn(Hkv, D, generator=g).to(torch.bfloat16)
+        case["v_cache"][blk, off] = torch.randn(Hkv, D, generator=g).to(torch.bfloat16)
+    d = to_dev(case)
+    kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
+    want = paged_attention_oracle(case["q"], kc_ref, vc_ref, case["k"], case["v"], case["cos"], case["sin"],
+                                  case["seqlens"], case["table"], case["scale"], causal=True, interleaved=False)
+    assert torch.isfinite(want).all()
+    got = b200ops.paged_attn_prefill(d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"], d["cos"], d["sin"],
+                                     d["seqlens"], d["table"], softmax_scale=case["scale"], variant=variant)
+    torch.cuda.synchronize()
+    assert torch.isfinite(got).all(), "NaN from never-written cache slots leaked into the output"
+    assert_close(got, want, what="prefill attention output (poisoned pool)")
