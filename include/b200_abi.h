@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 13
+#define B200_ABI_VERSION 14
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -119,6 +119,43 @@ int b200_greedy_argmax(const void* logits, int logits_dtype,
                        int64_t* out_ids,
                        void* workspace, int64_t workspace_bytes,
                        void* stream);
+
+/* Top-k / top-p sampling: replaces the reference's Inductor-compiled Sampler._sample_impl
+ * (/root/reference/core/layer/sampler.py:21-43; called with top_k = 50 for decode, 1000 for prefill,
+ * core/engine.py:233, :278) in ONE launch, one CTA per row:
+ *   x = logits / temperatures[row];  the top_k largest (ties: lowest token id), sorted descending;
+ *   probs = softmax(x) over them (fp32);  cum = cumsum(probs);  kept = cum < top_ps[row], first always kept;
+ *   renormalise;  draw = first kept candidate whose cumulative probability exceeds uniforms[row].
+ * `uniforms` f32 [rows] in [0, 1) comes from the caller's generator (the reference draws with
+ * torch.multinomial; the DISTRIBUTION is the contract, the RNG stream is not reproducible across
+ * implementations).  temperatures / top_ps / uniforms may be NULL (1.0 / 1.0 / 0.0: the arg-max).
+ * top_k in [1, 1024] (clamped to vocab).  Optional debug outputs for parity tests: dbg_idx i32 [rows, top_k]
+ * = candidate token ids in sorted order, dbg_prob f32 [rows, top_k] = renormalised probabilities (0 for the
+ * candidates the top-p mask removed); both NULL or both set.  out_ids i64 [rows].  No scratch; capturable. */
+int b200_topk_topp_sample(const void* logits, int logits_dtype, int64_t rows, int64_t vocab, int64_t stride,
+                          int top_k, const float* temperatures, const float* top_ps, const float* uniforms,
+                          int64_t* out_ids, int32_t* dbg_idx, float* dbg_prob, void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Device-resident decode metadata — replaces, between decode steps, the per-step rebuild of
+ * core/cache_manager.py:509-546 (cache_batch_data: B slice-assign kernels + 2 H2D copies) driven by
+ * core/engine.py:259-262:   cache_seqlens[0..B) += delta   and every pending block-table entry
+ * (KVCacheManager.append handing out a new page = one int32) is written from the device-side list
+ *   updates = int32 [1 + 3 * max_updates] = { count, (row, col, block_id) x count },
+ * whose count the kernel resets to 0.  The list is read at run time, so the launch may sit inside a captured
+ * CUDA graph.  updates may be NULL (lengths only).  One CTA.
+ * ------------------------------------------------------------------------ */
+int b200_table_advance(int32_t* cache_seqlens, int B, int delta, int32_t* block_table, int64_t bt_stride,
+                       int rows, int cols, int32_t* updates, int max_updates, void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * L2 prefetch of `rows` slabs of `row_bytes` bytes, `stride_bytes` apart, starting at ptr (rows = 1: one contiguous
+ * range) (cp.async.bulk.prefetch.L2; reads nothing into the SM, writes nothing).  The
+ * decode runner launches it on a side stream beside the NVLink reduction after o_proj / down_proj
+ * (core/layer/model_graph.py:210, :219), a latency-bound kernel that leaves HBM idle, with the weights of the GEMM
+ * that follows the reduction.  ptr and stride 16-byte aligned; at most 64 CTAs.
+ * ------------------------------------------------------------------------ */
+int b200_l2_prefetch(const void* ptr, int64_t row_bytes, int64_t rows, int64_t stride_bytes, void* stream);
 
 /* ------------------------------------------------------------------------ *
  * Weight-streaming GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, swap-AB:

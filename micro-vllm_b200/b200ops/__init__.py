@@ -18,7 +18,7 @@ from ._lib import B200Error, DecodeArgs, PrefillArgs, lib, check, LIB_PATH  # no
 
 __all__ = [
     "swiglu", "rmsnorm", "rmsnorm_residual", "store_kvcache", "paged_attn_decode",
-    "paged_attn_prefill", "lse_combine", "greedy_argmax", "skinny_gemm", "skinny_gemm_ok", "stream_gemm", "stream_gemm_ok", "interleave_up_gate", "decode_num_splits", "decode_use_balanced", "decode_algorithmic_bytes", "reserve_graph_workspace", "B200Error", "LIB_PATH",
+    "paged_attn_prefill", "lse_combine", "greedy_argmax", "topk_topp_sample", "skinny_gemm", "skinny_gemm_ok", "stream_gemm", "stream_gemm_ok", "interleave_up_gate", "decode_num_splits", "decode_use_balanced", "decode_algorithmic_bytes", "reserve_graph_workspace", "l2_prefetch", "table_advance", "B200Error", "LIB_PATH",
 ]
 
 
@@ -96,6 +96,46 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
                                  k_cache.shape[0], block_size,
                                  k_cache.stride(0), k_cache.stride(1), k_cache.stride(2), _stream()),
           "b200_store_kvcache")
+
+
+def table_advance(cache_seqlens: torch.Tensor, batch: int, delta: int = 1, block_table: Optional[torch.Tensor] = None,
+                  updates: Optional[torch.Tensor] = None) -> None:
+    """cache_seqlens[:batch] += delta and apply the pending block-table entries of the device-side list
+    ``updates`` = int32 ``[count, (row, col, block) * count]`` (count is reset to 0).  Current stream; capturable."""
+    _req_cuda(cache_seqlens, block_table, updates)
+    assert cache_seqlens.dtype == torch.int32 and cache_seqlens.is_contiguous() and cache_seqlens.numel() >= batch
+    bt_ptr, stride, rows, cols, up_ptr, max_up = None, 0, 0, 0, None, 0
+    if updates is not None:
+        assert block_table is not None and block_table.dtype == torch.int32 and block_table.stride(1) == 1
+        assert updates.dtype == torch.int32 and updates.is_contiguous() and updates.numel() >= 4
+        bt_ptr, stride, (rows, cols) = block_table.data_ptr(), block_table.stride(0), block_table.shape
+        up_ptr, max_up = updates.data_ptr(), (updates.numel() - 1) // 3
+    check(lib.b200_table_advance(cache_seqlens.data_ptr(), int(batch), int(delta), bt_ptr, stride, rows, cols,
+                                 up_ptr, max_up, _stream()), "b200_table_advance")
+
+
+def l2_prefetch(t: torch.Tensor, nbytes: Optional[int] = None, per_row: bool = False) -> None:
+    """Ask the memory system to bring ``nbytes`` of the 2-D row-major tensor ``t`` (all of it by default) into L2
+    (current stream; capturable; touches no data): the first ``nbytes`` of its storage, or — ``per_row`` — the
+    first ``nbytes / rows`` bytes of EVERY row (what a GEMM that walks the rows' leading columns first reads)."""
+    _req_cuda(t)
+    assert t.dim() == 2 and t.stride(1) == 1, "l2_prefetch: 2-D, last dim contiguous"
+    es = t.element_size()
+    rows, row_bytes, stride = t.shape[0], t.shape[1] * es, t.stride(0) * es
+    total = rows * row_bytes
+    n = total if nbytes is None else max(0, min(int(nbytes), total))
+    if n == 0:
+        return
+    if stride == row_bytes and (not per_row or n == total):
+        check(lib.b200_l2_prefetch(t.data_ptr(), n & ~15, 1, 0, _stream()), "b200_l2_prefetch")
+    elif per_row:
+        per = (n // rows) & ~127
+        if per:
+            check(lib.b200_l2_prefetch(t.data_ptr(), per, rows, stride, _stream()), "b200_l2_prefetch")
+    else:
+        full = n // row_bytes
+        if full:
+            check(lib.b200_l2_prefetch(t.data_ptr(), row_bytes & ~15, full, stride, _stream()), "b200_l2_prefetch")
 
 
 # ------------------------------------------------------------------ decode attention
@@ -364,6 +404,34 @@ def greedy_argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
     check(lib.b200_greedy_argmax(logits.data_ptr(), _wdt(logits), rows, vocab, logits.stride(0) if rows > 1 else max(logits.stride(0), vocab),
                                  out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "b200_greedy_argmax")
     return out[:rows]
+
+
+def topk_topp_sample(logits: torch.Tensor, temperatures: Optional[torch.Tensor], top_ps: Optional[torch.Tensor],
+                     top_k: int, uniforms: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                     debug: bool = False):
+    """The reference sampler body (core/layer/sampler.py:21-43) in one launch: top-k of ``logits / temp``, softmax,
+    top-p prefix mask (first candidate always kept), renormalise, inverse-CDF draw with ``uniforms [rows]`` in [0, 1)
+    (``None`` -> 0: the arg-max).  ``debug`` also returns (candidate ids [rows, k] int32 sorted by probability,
+    renormalised probabilities [rows, k] fp32) — what the parity tests compare with the eager restatement."""
+    _req_cuda(logits, temperatures, top_ps, uniforms, out)
+    assert logits.dim() == 2 and logits.stride(1) == 1, "topk_topp_sample: [rows, vocab], last dim contiguous"
+    assert logits.dtype in (torch.bfloat16, torch.float32), "topk_topp_sample: bf16 / fp32 logits"
+    rows, vocab = logits.shape
+    k = min(int(top_k), vocab)
+    for name, t in (("temperatures", temperatures), ("top_ps", top_ps), ("uniforms", uniforms)):
+        assert t is None or (t.dtype == torch.float32 and t.is_contiguous() and t.numel() == rows), \
+            f"topk_topp_sample: {name} must be fp32 [rows]"
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == rows
+    di = torch.empty((rows, k), dtype=torch.int32, device=logits.device) if debug else None
+    dp = torch.empty((rows, k), dtype=torch.float32, device=logits.device) if debug else None
+    ptr = lambda t: t.data_ptr() if t is not None else None
+    check(lib.b200_topk_topp_sample(logits.data_ptr(), _wdt(logits), rows, vocab,
+                                    logits.stride(0) if rows > 1 else max(logits.stride(0), vocab), k,
+                                    ptr(temperatures), ptr(top_ps), ptr(uniforms), out.data_ptr(), ptr(di), ptr(dp),
+                                    _stream()), "b200_topk_topp_sample")
+    return (out, di, dp) if debug else out
 
 
 # ------------------------------------------------------------------ decode-sized GEMM (tcgen05)

@@ -73,8 +73,21 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile every .cu for sm_100a and link libb200ops.so; returns its path."""
     if not force and is_fresh():
         return LIB_PATH
-    nvcc = _nvcc()
     os.makedirs(OBJ_DIR, exist_ok=True)
+    # one builder at a time (torchrun starts every rank at once): the others wait, then find the fresh library
+    import fcntl
+    with open(os.path.join(OBJ_DIR, "lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_fresh():
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
+    nvcc = _nvcc()
     srcs = sources()
 
     def compile_one(src: str) -> str:
@@ -92,10 +105,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=min(len(srcs), os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, srcs))
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs]      # static cudart: self-contained .so
+    tmp = LIB_PATH + f".{os.getpid()}.tmp"
+    cmd = [nvcc, "-shared", "-o", tmp, *objs]           # static cudart: self-contained .so
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp, LIB_PATH)                           # a reader never sees a half-written library
     deps = srcs + _headers()
     with open(os.path.join(OBJ_DIR, "stamp"), "w") as f:
         f.write(_digest(deps))

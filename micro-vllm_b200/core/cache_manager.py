@@ -96,6 +96,16 @@ class KVCacheManager:
             self._stages.append({"bt": bt, "sl": sl, "bt_np": bt.numpy(), "sl_np": sl.numpy(), "event": None})
         self._stage_idx = 0
         self.len_max_over_mean = 1.0
+        # Device-resident metadata between decode steps: a small device-side update list
+        # [count, (row, col, block) * n] that b200_table_advance applies, and its pinned double-buffered mirror
+        self.max_table_updates = 4 * max_batch_size
+        self._updates_dev = torch.zeros(1 + 3 * self.max_table_updates, dtype=torch.int32, device=device) \
+            if self._on_gpu else None
+        self._upd_stages = []
+        for _ in range(2):
+            up = torch.zeros(1 + 3 * self.max_table_updates, dtype=torch.int32, pin_memory=self._on_gpu)
+            self._upd_stages.append({"t": up, "np": up.numpy(), "event": None})
+        self._upd_idx = 0
 
     # ------------------------------------------------------------------ allocator
     def alloc(self, seq_id: int, n_tokens: int) -> Tuple[bool, Optional[torch.Tensor]]:
@@ -204,6 +214,47 @@ class KVCacheManager:
                     stage["event"] = torch.cuda.Event()
                 stage["event"].record()
         return self._block_table_buffer[:B], self._cache_seqlens_buffer[:B]
+
+    def append_on_device(self, seq_ids: list, steps: int = 1) -> int:
+        """Run ``append`` ``steps`` times for every sequence of the batch on the host (the allocator state stays
+        exactly the reference's, cache_manager.py:401-438) and ship ONLY what changed to the device: each page the
+        calls handed out is one ``(row, column, block id)`` entry of the device-side update list that
+        ``b200_table_advance`` applies (one small async H2D, none at all when no page boundary was crossed).
+        The sequence lengths are NOT uploaded: they advance on the device (``advance_lengths`` or the in-graph
+        launch of a multi-step decode graph).  Rows must already be laid out by ``cache_batch_data`` in this order.
+        Returns the number of new pages; -1 if the pool ran dry (like ``append``)."""
+        assert self._on_gpu, "append_on_device: CUDA cache manager only"
+        ups = []
+        for row, sid in enumerate(seq_ids):
+            blocks = self._blocks.get(sid)
+            if blocks is None:
+                return -1
+            before = len(blocks)
+            for _ in range(steps):
+                if self.append(sid) < 0:
+                    return -1
+            for col in range(before, len(blocks)):
+                if col >= self.max_seq_blocks:
+                    raise ValueError("sequence outgrew the block table")
+                ups.append((row, col, blocks[col]))
+        if ups:
+            assert len(ups) <= self.max_table_updates, "too many new pages for one update list"
+            st = self._upd_stages[self._upd_idx]
+            self._upd_idx ^= 1
+            if st["event"] is not None:
+                st["event"].synchronize()
+            st["np"][0] = len(ups)
+            st["np"][1:1 + 3 * len(ups)] = np.asarray(ups, dtype=np.int32).reshape(-1)
+            self._updates_dev[:1 + 3 * len(ups)].copy_(st["t"][:1 + 3 * len(ups)], non_blocking=True)
+            if st["event"] is None:
+                st["event"] = torch.cuda.Event()
+            st["event"].record()
+        return len(ups)
+
+    def advance_lengths(self, batch_size: int, delta: int = 1) -> None:
+        """``cache_seqlens[:B] += delta`` and apply pending table updates, on the device (one tiny launch)."""
+        import b200ops
+        b200ops.table_advance(self._cache_seqlens_buffer, batch_size, delta, self._block_table_buffer, self._updates_dev)
 
     def get_buffer_data(self, seq_ids: list):
         B = len(seq_ids)

@@ -90,6 +90,12 @@ class ModelGraphRunner:
         self._stream_mode = os.environ.get("B200_STREAM_GEMM", "auto")
         self._stream = self._stream_mode != "0" and torch.device(device).type == "cuda"
         self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "0") == "1"
+        # TP only: while the NVLink reduction after o_proj / down_proj runs (a latency-bound kernel on a handful of SMs
+        # that leaves HBM idle), a side stream asks L2 for the weights of the GEMMs behind it (b200_l2_prefetch), so the
+        # reduction's latency is paid in parallel with weight bytes that have to come from HBM anyway.
+        # B200_AR_PREFETCH_MB = how many MB per reduction (0 = off).
+        self._prefetch_bytes = int(float(os.environ.get("B200_AR_PREFETCH_MB", "48")) * 1e6) if self.world_size > 1 else 0
+        self._side_stream = None
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
         self.rope = RoPE()
@@ -97,6 +103,8 @@ class ModelGraphRunner:
         self._alloc_bufs()
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self._graphs_balanced: Dict[int, torch.cuda.CUDAGraph] = {}
+        self._graphs_multi: Dict[tuple, torch.cuda.CUDAGraph] = {}
+        self._tok_hist = None
         self._is_graph_ready = False
 
     # ------------------------------------------------------------------ init
@@ -127,14 +135,22 @@ class ModelGraphRunner:
                 b_q, b_k, b_v = bias.split([q_dim, kv_dim, kv_dim], dim=0)
                 block.attn._qkv_b = torch.cat([b.chunk(ws, dim=0)[r] for b in (b_q, b_k, b_v)], dim=0)
             if self._stream:
-                # nn.Linear layout ([out, in], K contiguous) per-rank slices for b200_stream_gemm; at TP = 1 the q/k/v, o and
-                # down matrices are the model's own tensors (no copy); gate_up is interleaved row-wise (up_j, gate_j)
+                # nn.Linear layout ([out, in], K contiguous) per-rank slices for b200_stream_gemm, built only for the
+                # products the policy sends there; at TP = 1 the q/k/v, o and down matrices are the model's own tensors
+                # (no copy); gate_up is interleaved row-wise (up_j, gate_j).
                 # (`.data`: plain tensors that keep the storage alive even if a caller later rebinds the Parameter)
-                block.attn._qkv_nk = (block.attn.c_attn.weight.data if ws == 1 else
-                                      torch.cat([w.chunk(ws, dim=0)[r] for w in (w_q, w_k, w_v)], dim=0).contiguous())
-                block.attn._o_nk = block.attn.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
-                block.mlp._d_nk = block.mlp.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
-                block.mlp._gu_nk = b200ops.interleave_up_gate(w1.chunk(ws, dim=0)[r], w2.chunk(ws, dim=0)[r])
+                def want(n, k):
+                    return self._stream_mode == "1" or k >= 4 * n
+                H = block.attn.c_attn.weight.shape[1]
+                if want((q_dim + 2 * kv_dim) // ws, H):
+                    block.attn._qkv_nk = (block.attn.c_attn.weight.data if ws == 1 else
+                                          torch.cat([w.chunk(ws, dim=0)[r] for w in (w_q, w_k, w_v)], dim=0).contiguous())
+                if want(H, q_dim // ws):
+                    block.attn._o_nk = block.attn.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
+                if want(H, w1.shape[0] // ws):
+                    block.mlp._d_nk = block.mlp.c_proj.weight.data.chunk(ws, dim=1)[r].contiguous()
+                if want(2 * w1.shape[0] // ws, H):
+                    block.mlp._gu_nk = b200ops.interleave_up_gate(w1.chunk(ws, dim=0)[r], w2.chunk(ws, dim=0)[r])
 
     def _alloc_bufs(self):
         mb, dev, dt = self.max_bs, self.device, self.dtype
@@ -247,6 +263,41 @@ class ModelGraphRunner:
             return b200ops.stream_gemm(x, w, out=self._logits[:x.shape[0]], pdl=self._stream_pdl)
         return head(x)
 
+    # ------------------------------------------------------------------ weight prefetch beside the reductions
+    def _prefetch_fork(self, weights):
+        """Start pulling ``weights`` (list of (tensor, per_row)) into L2 on the side stream, ordered after everything
+        already queued on the current stream (the GEMM whose output is about to be reduced).  Returns True if a join
+        is owed."""
+        budget = self._prefetch_bytes
+        if budget <= 0 or not weights:
+            return False
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=self.device)
+        cur = torch.cuda.current_stream()
+        self._side_stream.wait_stream(cur)
+        with torch.cuda.stream(self._side_stream):
+            for w, per_row in weights:
+                if budget <= 0 or w is None:
+                    continue
+                n = min(budget, w.numel() * w.element_size())
+                b200ops.l2_prefetch(w, n, per_row=per_row)
+                budget -= n
+        return True
+
+    def _prefetch_join(self, owed):
+        if owed:
+            torch.cuda.current_stream().wait_stream(self._side_stream)
+
+    def _gemm_weight(self, mod, nk_name, kn_name, bs):
+        """(tensor, per_row) the GEMM of this module will stream for a batch of ``bs`` rows: the nn.Linear-layout slice
+        when the stream GEMM takes the product (stream-K shares are contiguous per CTA: prefetch a k-slab of every
+        row), else the reference-layout [in, out] matrix for cuBLAS (tiles walk k from row 0: prefetch a prefix)."""
+        w_nk = getattr(mod, nk_name, None)
+        if self._use_stream(bs, w_nk):
+            full = w_nk.numel() * w_nk.element_size() <= self._prefetch_bytes
+            return (w_nk, not full)
+        return (getattr(mod, kn_name), False)
+
     # ------------------------------------------------------------------ decode step
     def _reduce_add_norm(self, slot, x, residual, norm, y, res_out, ss_rounded):
         """res_out = all_reduce(x) + residual;  y = rmsnorm(res_out) * norm.weight — one launch.
@@ -275,13 +326,25 @@ class ModelGraphRunner:
             block = tr.h[layer_idx]
             qkv = self._qkv_proj(block, bs)
             attn_out = self._flash_attn(qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced)
+            owed = self._prefetch_fork([self._gemm_weight(block.mlp, "_gu_nk", "_gu", bs)]) if self._comm is not None else False
             # all_reduce + rmsnorm_residual_gemm (reference :210-216): sum of squares of the unrounded sum
             self._reduce_add_norm(0, attn_out, h, block.ln_2, normed, residual, ss_rounded=False)
+            self._prefetch_join(owed)
             mlp_out = self._ffn(normed, block, bs)
             # all_reduce(mlp_out).add_(residual) + the next rmsnorm_ (reference :219, :143 / :222)
             last = layer_idx + 1 == self.num_layers
             nxt = (ln_f if fuse_ln_f else None) if last else tr.h[layer_idx + 1].ln_1
+            owed = False
+            if self._comm is not None:
+                if last:
+                    lw = getattr(self.model.lm_head, "weight", None)
+                    owed = self._prefetch_fork([(lw.data, False)] if lw is not None and lw.dim() == 2 and lw.is_contiguous() else [])
+                else:
+                    nb = tr.h[layer_idx + 1]
+                    owed = self._prefetch_fork([self._gemm_weight(nb.attn, "_qkv_nk", "_qkv_w", bs),
+                                                self._gemm_weight(nb.attn, "_o_nk", "_o", bs)])
             self._reduce_add_norm(1, mlp_out, residual, nxt, normed, h_buf, ss_rounded=True)
+            self._prefetch_join(owed)
             h = h_buf
         return self._lm_head(normed if fuse_ln_f else ln_f(h))
 
@@ -349,6 +412,57 @@ class ModelGraphRunner:
                                    balanced=ragged and batch_size <= 512)
         g.replay()
         return self._logits[:batch_size]
+
+    # ------------------------------------------------------------------ several greedy steps in ONE graph
+    def capture_multistep(self, cache_manager, batch_size: int, steps: int):
+        """Capture ``steps`` greedy decode steps of ``batch_size`` rows as ONE CUDA graph.  Between the steps nothing
+        returns to the host: the greedy ids (``b200_greedy_argmax``) feed the next step's input on the device, the
+        sequence lengths advance on the device and the pages the steps will need are written into the device block
+        table by the graph's first node from the update list ``KVCacheManager.append_on_device`` uploaded
+        (``b200_table_advance``).  Replaces ``steps`` round trips of engine.py:248-286 (append + cache_batch_data +
+        replay + sampler + broadcast)."""
+        bs = batch_size
+        key = (bs, steps)
+        if key in self._graphs_multi:
+            return
+        if self._tok_hist is None or self._tok_hist.shape[0] < steps:
+            self._tok_hist = torch.zeros((max(steps, 16), self.max_bs), dtype=torch.long, device=self.device)
+        seqlens, table = cache_manager._cache_seqlens_buffer, cache_manager._block_table_buffer
+        dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
+        with torch.no_grad():
+            for _ in range(3):                                   # eager warm-up against the all-zero table, as capture()
+                lg = self.decode(dummy, bs, cache_manager, use_graph_cache=False)
+                b200ops.greedy_argmax(lg, self._next_ids[:bs])
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(g):
+            b200ops.table_advance(seqlens, bs, 0, table, cache_manager._updates_dev)    # pages handed out by the host
+            for s in range(steps):
+                lg = self.decode(self._input_ids[:bs], bs, cache_manager, use_graph_cache=True)
+                if lg.data_ptr() != self._logits.data_ptr():
+                    self._logits[:bs] = lg
+                b200ops.greedy_argmax(self._logits[:bs], self._next_ids[:bs])
+                self._tok_hist[s, :bs].copy_(self._next_ids[:bs])
+                self._input_ids[:bs].copy_(self._next_ids[:bs])
+                b200ops.table_advance(seqlens, bs, 1)              # the token just cached is part of the context now
+        self._graphs_multi[key] = g
+
+    def forward_greedy_multistep(self, input_ids: torch.Tensor, cache_manager, seq_ids: list, steps: int) -> torch.Tensor:
+        """``steps`` greedy decode steps for the sequences ``seq_ids`` (rows of the batch in this order, lengths and
+        table already on the device from ``cache_batch_data``): host allocator bookkeeping for all steps, ONE small
+        upload of the new pages (if any), ONE graph replay.  Returns the ids ``[batch, steps]`` (a view of a static
+        buffer); the device lengths have advanced by ``steps``."""
+        bs = len(seq_ids)
+        key = (bs, steps)
+        if key not in self._graphs_multi:
+            self.capture_multistep(cache_manager, bs, steps)
+        if self._comm is not None:
+            self._comm.poll_error()
+        if cache_manager.append_on_device(seq_ids, steps) < 0:
+            raise RuntimeError("OOM: KV cache pool exhausted")           # engine.py:220 convention
+        self._input_ids[:bs] = input_ids
+        self._graphs_multi[key].replay()
+        return self._tok_hist[:steps, :bs].t()
 
     def forward_greedy(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
         """One decode step returning the greedy next-token ids ``[batch_size]`` int64 (a view of a static

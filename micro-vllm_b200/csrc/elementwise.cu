@@ -295,9 +295,78 @@ store_kvcache_scalar_kernel(const __nv_bfloat16* __restrict__ key, const __nv_bf
     }
 }
 
+// ============================================================== device-resident block table
+// One tiny launch keeps the decode metadata on the device between steps:  cache_seqlens[:B] += delta  and the
+// pending block-table entries (a page handed out by KVCacheManager.append = ONE int32 write) are applied from a
+// device-side update list  updates = [count, (row, col, block) x count]  whose count the kernel zeroes again.
+// The list is read from device memory at run time, so the launch can sit inside a captured CUDA graph (the first
+// node of a multi-step decode graph) while the host only uploads the few entries that changed.
+__global__ void __launch_bounds__(256)
+table_advance_kernel(int32_t* __restrict__ seqlens, int B, int delta, int32_t* __restrict__ table, int64_t bt_stride,
+                     int rows, int cols, int32_t* __restrict__ updates, int max_updates) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (updates != nullptr) {
+        int n = updates[0];
+        if (n > max_updates) n = max_updates;
+        for (int i = tid; i < n; i += gridDim.x * blockDim.x) {
+            const int r = updates[1 + 3 * i], c = updates[2 + 3 * i], blk = updates[3 + 3 * i];
+            if (r >= 0 && r < rows && c >= 0 && c < cols) table[(int64_t)r * bt_stride + c] = blk;
+        }
+    }
+    if (delta != 0)
+        for (int i = tid; i < B; i += gridDim.x * blockDim.x) seqlens[i] += delta;
+    if (updates != nullptr) {
+        __syncthreads();                       // single CTA (see the launch): every thread has read the count
+        if (tid == 0) updates[0] = 0;
+    }
+}
+
+// ============================================================== L2 prefetch
+// Pulls `rows` slabs of `row_bytes` bytes, `stride` bytes apart, into L2 with bulk prefetches (no registers, no shared
+// memory, nothing written): the decode runner launches it on a side stream next to the NVLink reduction — a
+// latency-bound kernel that leaves HBM idle — so that the weights of the GEMM behind the reduction are already on
+// their way (core/layer/model_graph.py).
+__global__ void __launch_bounds__(256)
+l2_prefetch_kernel(const uint8_t* __restrict__ base, int64_t row_bytes, int64_t rows, int64_t stride, int chunk) {
+    const int64_t cpr = (row_bytes + chunk - 1) / chunk;
+    const int64_t n_chunks = cpr * rows;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_chunks; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / cpr, off = (i - r * cpr) * chunk;
+        const uint32_t sz = (uint32_t)((row_bytes - off < chunk) ? (row_bytes - off) & ~15LL : chunk);
+        if (sz) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(base + r * stride + off), "r"(sz) : "memory");
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_table_advance(int32_t* cache_seqlens, int B, int delta, int32_t* block_table, int64_t bt_stride,
+                                  int rows, int cols, int32_t* updates, int max_updates, void* stream) {
+    if (B < 0 || (B > 0 && !cache_seqlens)) B200_FAIL(B200_E_NULL, "table_advance: cache_seqlens is NULL");
+    if (updates && (!block_table || max_updates < 0 || rows < 0 || cols < 0 || bt_stride < cols))
+        B200_FAIL(B200_E_RANGE, "table_advance: update list without a block table (rows=%d cols=%d stride=%lld)", rows, cols, (long long)bt_stride);
+    if (B == 0 && !updates) return 0;
+    table_advance_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(cache_seqlens, B, delta, block_table, bt_stride, rows, cols,
+                                                              updates, max_updates);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int b200_l2_prefetch(const void* ptr, int64_t row_bytes, int64_t rows, int64_t stride_bytes, void* stream) {
+    if (!ptr) B200_FAIL(B200_E_NULL, "l2_prefetch: null pointer");
+    if (row_bytes < 0 || rows < 0 || (rows > 1 && stride_bytes < row_bytes))
+        B200_FAIL(B200_E_RANGE, "l2_prefetch: row_bytes=%lld rows=%lld stride=%lld", (long long)row_bytes, (long long)rows, (long long)stride_bytes);
+    if (!aligned16(ptr) || (rows > 1 && stride_bytes % 16)) B200_FAIL(B200_E_ALIGN, "l2_prefetch: pointer / stride must be 16-byte aligned");
+    if (row_bytes < 16 || rows == 0) return 0;
+    const int chunk = 2048;
+    const int64_t n_chunks = ((row_bytes + chunk - 1) / chunk) * rows;
+    int64_t blocks = (n_chunks + 255) / 256;
+    if (blocks > 64) blocks = 64;                        // a sliver of the chip: the kernels it runs beside need the rest
+    l2_prefetch_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)ptr, row_bytes, rows, stride_bytes, chunk);
+    B200_CHECK_LAUNCH();
+    return 0;
+}
 
 extern "C" int b200_version(void) { return B200_ABI_VERSION; }
 extern "C" const char* b200_last_error(void) { return g_err; }

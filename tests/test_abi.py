@@ -151,8 +151,19 @@ def test_sampler_and_new_ops_refuse_cpu_and_unsupported_modes():
     from core.layer.sampler import Sampler
     logits = torch.zeros(2, 64, dtype=torch.bfloat16)
     ones = torch.ones(2)
-    with pytest.raises(NotImplementedError):                # stochastic sampling is outside the hot-path scope
+    with pytest.raises(AssertionError):                     # top-k / top-p: CUDA tensors only, no fallback
         Sampler()(logits, ones, ones, 50)
+    with pytest.raises(AssertionError):
+        b200ops.topk_topp_sample(logits, ones, ones, 50)
+    lib = b200ops._lib.lib
+    E = b200ops._lib
+    assert lib.b200_topk_topp_sample(None, 0, 1, 8, 8, 4, None, None, None, None, None, None, None) == E.E_NULL
+    assert lib.b200_topk_topp_sample(0x1000, 0, 1, 8, 4, 4, None, None, None, 0x1000, None, None, None) == E.E_RANGE
+    assert lib.b200_topk_topp_sample(0x1000, 0, 1, 8, 8, 0, None, None, None, 0x1000, None, None, None) == E.E_RANGE
+    assert lib.b200_topk_topp_sample(0x1000, 0, 1, 8, 8, 1025, None, None, None, 0x1000, None, None, None) == E.E_RANGE
+    assert lib.b200_topk_topp_sample(0x1000, 7, 1, 8, 8, 4, None, None, None, 0x1000, None, None, None) == E.E_UNSUPPORTED
+    assert lib.b200_topk_topp_sample(0x1000, 0, 1, 8, 8, 4, None, None, None, 0x1000, 0x1000, None, None) == E.E_NULL
+    assert lib.b200_topk_topp_sample(0x1000, 0, 0, 8, 8, 4, None, None, None, 0x1000, None, None, None) == 0   # no rows
     with pytest.raises(AssertionError):                     # greedy: CUDA tensors only, no fallback
         Sampler()(logits, ones, ones, 1)
     with pytest.raises(AssertionError):

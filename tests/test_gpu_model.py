@@ -227,3 +227,69 @@ def test_ragged_batch_replays_balanced_graph():
     spread = out[False].std().item()
     assert (out[True][0] - out[False][0]).abs().max().item() < 0.05 * spread      # step 0: identical inputs
     assert torch.equal(out[True][0].argmax(-1), out[False][0].argmax(-1))
+
+
+def test_multistep_greedy_graph_matches_single_steps():
+    """K greedy steps in ONE graph (ids fed back on the device, lengths advanced on the device, new
+    pages applied from the device-side update list) == K engine-style single steps (append + cache_batch_data +
+    replay per step).  The run crosses the 255/256 page boundary inside a multi-step graph, and the host
+    allocator must end in the state the reference's own sequence of append calls produces (oracle)."""
+    shape = SHAPES["qwen2.5-0.5b"]
+    L, P, K, rounds, B = 4, 247, 8, 3, 2
+    model, dec, pre, mgr = make_runners(shape, L, max_bs=B, seed=3, std=0.01, peaky=True, vocab=8192)
+    g = torch.Generator().manual_seed(9)
+    prompt = torch.randint(0, 8192, (B, P), generator=g)
+    ids = list(range(B))
+
+    def prefill():
+        mgr.reset()
+        for lyr in range(L):
+            mgr.k_caches[lyr].zero_()
+            mgr.v_caches[lyr].zero_()
+        for s_ in ids:
+            assert mgr.alloc(s_, P)[0]
+        mgr.cache_batch_data(ids, [P] * B)
+        with torch.no_grad():
+            logits = pre.forward(prompt.cuda(), mgr, B)
+        return logits[:, -1, :].float().argmax(-1)
+
+    # (a) single steps, engine style
+    dec.capture(mgr, batch_sizes=[B], greedy=True)
+    tok = prefill()
+    single, pos = [], P + 1
+    for _ in range(K * rounds):
+        for s_ in ids:
+            mgr.append(s_)
+        mgr.cache_batch_data(ids, [pos] * B)
+        tok = dec.forward_greedy(tok, mgr, B).clone()
+        single.append(tok.cpu())
+        pos += 1
+    single = torch.stack(single, 1)
+    state_single = (list(mgr._free), {k: list(v) for k, v in mgr._blocks.items()}, dict(mgr._pos))
+    k_single = [mgr.k_caches[lyr].clone() for lyr in range(L)]
+    # (b) K steps per graph replay
+    tok = prefill()
+    mgr.cache_batch_data(ids, [P + 1] * B)            # first decode position (sequence.py:17,42), once
+    multi = []
+    for _ in range(rounds):
+        out = dec.forward_greedy_multistep(tok, mgr, ids, K).clone()
+        multi.append(out.cpu())
+        tok = out[:, -1].clone()
+    multi = torch.cat(multi, 1)
+    torch.cuda.synchronize()
+    assert multi.tolist() == single.tolist(), "multi-step graph diverged from single steps"
+    assert mgr._cache_seqlens_buffer[:B].tolist() == [P + 1 + K * rounds] * B
+    assert (list(mgr._free), {k: list(v) for k, v in mgr._blocks.items()}, dict(mgr._pos)) == state_single
+    assert len(mgr._blocks[0]) == 2, "the run must have crossed a page boundary"
+    bt = mgr._block_table_buffer[:B, :2].cpu()
+    assert bt.tolist() == [mgr._blocks[s_][:2] for s_ in ids]
+    for lyr in range(L):
+        assert torch.equal(mgr.k_caches[lyr], k_single[lyr]), "cache contents must match the single-step run bit for bit"
+    # allocator parity against the oracle restatement of the reference class
+    orc = AllocatorOracle(40, 256, max_tokens=1024, max_batch_size=B)
+    for s_ in ids:
+        orc.alloc(s_, P)
+    for _ in range(K * rounds):
+        for s_ in ids:
+            orc.append(s_)
+    assert orc.snapshot() == {"free": state_single[0], "blocks": state_single[1], "pos": state_single[2]}

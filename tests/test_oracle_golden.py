@@ -182,3 +182,33 @@ def test_elementwise_oracle_matches_triton_golden(golden_dir):
             close(y, rec["y"], name)
             assert all(rec["variants_equal"])
     assert kinds == {"swiglu", "rmsnorm", "rmsnorm_residual"}
+
+
+def sampler_dense(ids, probs, vocab):
+    """[B, k] candidates -> dense [B, vocab] probability rows (position inside a group of equal values is free)."""
+    out = torch.zeros(ids.shape[0], vocab, dtype=torch.float64)
+    out.scatter_(1, ids.long(), probs.double())
+    return out
+
+
+def test_sampler_oracle_matches_reference_golden(golden_dir):
+    """oracle/sampling.py against the outputs of the reference's own ``Sampler._sample_impl``
+    (core/layer/sampler.py:21-43; generated by tests/golden/make_golden_sampler.py): the same candidate set, the
+    same renormalised probability for every token id (fp32 noise), the same draw for the stored uniform numbers."""
+    from oracle.sampling import sample_oracle
+    gold = torch.load(os.path.join(golden_dir, "sampler_reference.pt"), weights_only=False)
+    assert len(gold) >= 5
+    for c in gold:
+        ids, probs, draw = sample_oracle(c["logits"], c["temperatures"], c["top_ps"], c["top_k"], c["u"])
+        V = c["logits"].shape[1]
+        assert ids.shape == c["ref_ids"].shape, c["name"]
+        assert torch.equal(ids.sort(-1).values, c["ref_ids"].sort(-1).values), f"{c['name']}: candidate sets differ"
+        assert torch.allclose(sampler_dense(ids, probs, V), sampler_dense(c["ref_ids"], c["ref_probs"], V),
+                              rtol=1e-5, atol=1e-7), c["name"]
+        assert torch.equal((probs > 0).sum(-1), (c["ref_probs"] > 0).sum(-1)), f"{c['name']}: top-p cut differs"
+        # same token, or (bf16 rows) a token of exactly the same logit: the order inside a group of equal values is
+        # torch-internal in the reference and by ascending id in the restatement
+        lg = c["logits"].float()
+        assert torch.equal(lg.gather(1, draw[:, None]), lg.gather(1, c["ref_draw"][:, None])), f"{c['name']}: draw differs"
+        if c["logits"].dtype == torch.float32:
+            assert torch.equal(draw, c["ref_draw"]), f"{c['name']}: draw differs"

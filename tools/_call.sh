@@ -1,5 +1,6 @@
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_stream_gemm.py -x -q > gpurun_out/pytest_sgemm.log 2>&1; echo "pytest sgemm rc=$?"; tail -3 gpurun_out/pytest_sgemm.log
-for s in "64 1024 8192 none" "64 8192 1280 none" "64 8192 7168 swiglu" "64 28672 8192 none"; do timeout 60 python tools/trace_stream_gemm.py $s; done > gpurun_out/sgemm_trace.log 2>&1; cat gpurun_out/sgemm_trace.log | cut -c1-1500
-timeout 200 python tools/bench_stream_gemm.py --shape llama3-70b --tp 8 --batch 64 > gpurun_out/sgemm_l70tp8.log 2>&1; echo "rc=$?"; tail -5 gpurun_out/sgemm_l70tp8.log | cut -c1-600
-timeout 200 python tools/bench_stream_gemm.py --shape llama3-70b --tp 1 --batch 64 > gpurun_out/sgemm_l70tp1.log 2>&1; echo "rc=$?"; tail -5 gpurun_out/sgemm_l70tp1.log | cut -c1-500
+python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29571 tools/bench_allreduce.py 64,8,1 > gpurun_out/allreduce_tp2.log 2>&1; echo "ar rc=$?"; grep '^{' gpurun_out/allreduce_tp2.log | cut -c1-2500
+timeout 300 python -m pytest tests/test_gpu_allreduce_norm.py -x -q > gpurun_out/pytest_ar.log 2>&1; echo "pytest ar rc=$?"; tail -4 gpurun_out/pytest_ar.log
+for pf in 0 48; do
+B200_AR_PREFETCH_MB=$pf timeout 300 python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29575 tools/bench_decode_step.py --shape llama3-70b --layers 16 --batch 64 --ctx 8192 > gpurun_out/step_l70_tp2_pf$pf.log 2>&1; echo "step pf=$pf rc=$?"; grep '^{' gpurun_out/step_l70_tp2_pf$pf.log | cut -c1-600
+done

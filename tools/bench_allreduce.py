@@ -65,6 +65,7 @@ def main():
                                                  res_b if c & 1 == 0 else res_a, 1e-5, bool(c & 1))
 
         def time_graph(fn, reps=10):
+            comm._last_mode = None        # phases are separated by barriers: nobody still reads either slot
             fn()
             torch.cuda.synchronize()
             dist.barrier()
@@ -105,8 +106,7 @@ def main():
             yo.zero_()
             torch.cuda.synchronize()
             dist.barrier()
-            comm.allreduce_residual_rmsnorm(0, rows, n, resid, w, yo, ro, 1e-5, True, sharded=name == "sharded",
-                                            ll=name == "ll", nvls=name == "nvls")
+            comm._last_mode = None        # every rank is past the barrier above: nobody still reads either slot
             comm.allreduce_residual_rmsnorm(1, rows, n, resid, w, yo, torch.empty_like(ro), 1e-5, True,
                                             sharded=name == "sharded", ll=name == "ll", nvls=name == "nvls")  # slot alternation
             comm.allreduce_residual_rmsnorm(0, rows, n, resid, w, yo, ro, 1e-5, True, sharded=name == "sharded",
@@ -120,9 +120,26 @@ def main():
             dist.all_gather(ys, yo.contiguous())
             same = all(torch.equal(ys[0], t_) for t_ in ys)
             row[name + "_check"] = {"res_out_bad": bad_res, "y_bad": bad_y, "ranks_bit_identical_y": bool(same)}
+        if comm.has_multicast:
+            # which rounding does the switch apply to the fp32 sum?  zero residual: res_out IS the switch's bf16 sum
+            zero = torch.zeros(rows, n, dtype=torch.bfloat16, device=dev)
+            ro = torch.zeros_like(zero)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm._last_mode = None
+            comm.allreduce_residual_rmsnorm(0, rows, n, zero, w, yb, ro, 1e-5, True, nvls=True)
+            torch.cuda.synchronize()
+            dist.barrier()
+            rne = ref.bfloat16()
+            rtz = (ref.view(torch.int32) & -65536).view(torch.float32).bfloat16()
+            g_ = ro[own]
+            row["nvls_sum_rounding"] = {"equals_rne_of_fp32_sum": round(float((g_ == rne[own]).float().mean()), 5),
+                                        "equals_rtz_of_fp32_sum": round(float((g_ == rtz[own]).float().mean()), 5),
+                                        "max_ulp_vs_rne": int((g_.view(torch.int16).int() - rne[own].view(torch.int16).int()).abs().max()) if g_.numel() else 0}
         for name in modes:
             row[name + "_us"] = round(time_graph(lambda: fused(name)), 2)
             trace.zero_()
+            comm._last_mode = None
             fused(name, trace)
             torch.cuda.synchronize()
             dist.barrier()

@@ -16,7 +16,7 @@ sys.path[:0] = [os.path.join(ROOT, "micro-vllm_b200"), ROOT]
 import torch  # noqa: E402
 
 
-def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup=3, verbose=False):
+def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup=3, verbose=False, profile=False):
     import torch.distributed as dist
     from core import parallel_config as pc
     from core.cache_manager import KVCacheManager
@@ -100,7 +100,31 @@ def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup
            "setup_s": round(setup_s, 1),
            "allreduce": ("none (TP=1)" if world == 1 else
                          ("fused-" + runner._ar_mode) if runner._comm is not None else "nccl"),
-           "gemm": runner.gemm_policy()}
+           "gemm": runner.gemm_policy(), "ar_prefetch_MB": round(runner._prefetch_bytes / 1e6, 1)}
+    if profile:
+        # per-kernel table of the REAL TP run on rank 0 (torch.profiler / CUPTI around graph replays); under the
+        # profiler kernels are serialised less tightly, so compare SHARES
+        from torch.profiler import ProfilerActivity, profile as tprofile
+        with tprofile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            for _ in range(steps):
+                runner.forward(tok, mgr, batch)
+            torch.cuda.synchronize()
+        rows = []
+        for ev in prof.key_averages():
+            t = getattr(ev, "device_time_total", None)
+            if t is None:
+                t = getattr(ev, "cuda_time_total", 0)
+            if t and ev.device_type is not None and "cuda" in str(ev.device_type).lower():
+                rows.append({"kernel": ev.key[:110], "calls_per_step": ev.count / steps,
+                             "us_per_call": round(t / ev.count, 2), "us_per_layer": round(t / steps / layers, 2)})
+        rows.sort(key=lambda r_: -r_["us_per_layer"])
+        res["kernels"] = rows
+        res["kernel_busy_us_per_layer"] = round(sum(r_["us_per_layer"] for r_ in rows), 1)
+        res["us_per_layer_events"] = round(ms * 1e3 / layers, 2)
+        if rank == 0:
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", f"layer_real_{shape_name}_tp{world}_b{batch}.json"), "w") as f:
+                json.dump(res, f, indent=1)
     comm = getattr(runner, "_comm", None)
     if comm is not None:
         res["allreduce_timeout_flag"] = comm.error_flag()
@@ -122,8 +146,13 @@ if __name__ == "__main__":
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--ctx", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--profile", action="store_true", help="also write the per-kernel table of rank 0 (torch.profiler)")
     a = ap.parse_args()
-    run(a.shape, a.layers, a.batch, a.ctx, a.steps, verbose=True)
+    r = run(a.shape, a.layers, a.batch, a.ctx, a.steps, verbose=False, profile=a.profile)
+    if int(os.environ.get("RANK", 0)) == 0:
+        print(json.dumps({k: v for k, v in r.items() if k != "kernels"}), flush=True)
+        for row in r.get("kernels", [])[:14]:
+            print(f"{row['us_per_layer']:9.2f} us/layer  {row['us_per_call']:8.2f} us x {row['calls_per_step']:6.1f}  {row['kernel']}")
     import torch.distributed as dist
     if dist.is_initialized():
         dist.destroy_process_group()
