@@ -177,13 +177,20 @@ int b200_l2_prefetch(const void* ptr, int64_t row_bytes, int64_t rows, int64_t s
  * (replay safe).  grid_hint: 0 = one CTA per SM (never more: the CTAs wait on one another).
  * flags: B200_GEMM_FLAG_PDL launches with programmatic stream serialization: the first weight
  * boxes are requested before griddepcontrol.wait (precondition: the preceding kernel in the
- * stream writes neither w nor bias).
+ * stream writes neither w nor bias).  With PDL, B200_GEMM_FLAG_L2_AHEAD(n) also prefetches the
+ * next n weight boxes (16 KB each) of every CTA's share into L2 before the wait: when the
+ * preceding kernel idles in a cross-GPU reduction, HBM already streams this product's weights.
  * ------------------------------------------------------------------------ */
 #define B200_GEMM_EPI_NONE   0
 #define B200_GEMM_EPI_BIAS   1
 #define B200_GEMM_EPI_SWIGLU 2
 #define B200_GEMM_FLAG_PDL   1
+#define B200_GEMM_FLAG_L2_AHEAD(n) (((n) & 0xffff) << 8)
 int64_t b200_stream_gemm_workspace_bytes(int M, int64_t N, int grid_hint);
+/* debug only: uint64 [CTAs of the split-KV grid][8] device buffer the next b200_paged_attn_decode launches stamp with
+ * %globaltimer (entry, first loads issued, prologue done, first stage landed, loop done, partial written, exit,
+ * merge done); NULL = off.  tools/trace_decode.py */
+void b200_debug_decode_trace(void* dev_ptr);
 /* debug only: uint64 [grid][8] device buffer the next launches stamp with %globaltimer per CTA (NULL = off) */
 void b200_debug_stream_gemm_trace(void* dev_ptr);
 int b200_stream_gemm(const void* x, const void* w, const void* bias, void* out,
@@ -385,6 +392,11 @@ void b200_debug_prefill_trace(void* dev_buf);
 #define B200_AR_MAX_WORLD 8
 #define B200_AR_MAX_CTAS  1024
 
+/* OR-ed into `mode`: launch with programmatic stream serialization (the kernel's prologue overlaps the tail of the
+ * previous kernel of the stream; it waits for that kernel before reading x / residual).  Every form also releases a
+ * PDL-launched SUCCESSOR at its start, so a weight-streaming GEMM behind it fetches weights during the exchange. */
+#define B200_AR_FLAG_PDL 0x100
+
 typedef struct b200_ar_args {
     const void* x_peers[B200_AR_MAX_WORLD];  /* rank r's partial sums, bf16 [rows, n] (entry `rank` is local) */
     void*       flag_peers[B200_AR_MAX_WORLD]; /* rank r's flag array (entry `rank` is local)                 */
@@ -436,13 +448,23 @@ typedef struct b200_ar_args {
 /* NVLS form (in-switch reduction; the form SURVEY.md §8f N1 names): every rank's slab is bound to ONE multicast
  * object (cuMulticastCreate / cuMulticastBindMem; `x_mc`, `y_mc`, `flags_mc` are addresses inside its mapping).
  * Row ownership and the row-sharded residual contract are those of ROW_SHARDED.  The owner of a row reads the SUM
- * of the row over all ranks with multimem.ld_reduce (fp32 accumulation inside the NVSwitch, one bf16 rounding),
+ * of the row over all ranks with multimem.ld_reduce (fp32 accumulation inside the NVSwitch, one rounding to bf16
+ * by the switch's own rule: measured within 1 bf16 ulp of the exact sum, not always round-to-nearest-even),
  * adds its residual row, normalises, and multimem.st's y into EVERY rank's y buffer; the two flag hops are
  * multimem.red on monotonic counters (u32 words B200_AR_MAX_CTAS * (B200_AR_MAX_WORLD + 1) and + 32 of every
  * rank's flag region; local targets in epoch words [B200_AR_MAX_CTAS + 4 .. + 6], so `epoch` must hold
  * B200_AR_MAX_CTAS + 8 words).  grid = ceil(rows / world) CTAs per rank.  When the call returns on any rank every
  * owner has finished reading x: the x slot may be rewritten immediately (no slot alternation). */
 #define B200_AR_MODE_NVLS 4
+
+/* One-hop NVLS form: EVERY rank asks the switch for the sum of EVERY row (multimem.ld_reduce of the whole slot; at
+ * decode sizes that is ~1 MB per GPU, far below NVLink bandwidth), adds its residual, normalises and stores y
+ * LOCALLY.  One flag hop (the `ready` counter), no second hop, no trailing barrier: latency of one switch round
+ * trip at any world size.  Contract = the one-shot form's: residual / res_out are full replicated tensors, y is any
+ * local tensor, and CONSECUTIVE calls must read x from different slots.  The switch rounds the fp32 sum to bf16 with
+ * its own rule (measured: within 1 bf16 ulp of the exact sum, not round-to-nearest-even; tools/bench_allreduce.py),
+ * identically for every requester, so ranks stay bit-identical.  Needs x_mc and flags_mc. */
+#define B200_AR_MODE_NVLS_ONEHOP 8
 
 int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
 

@@ -452,14 +452,15 @@ def interleave_up_gate(up_w: torch.Tensor, gate_w: torch.Tensor) -> torch.Tensor
 
 def stream_gemm(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None,
                 bias: Optional[torch.Tensor] = None, swiglu: bool = False, pdl: bool = False,
-                grid: int = 0) -> torch.Tensor:
+                grid: int = 0, l2_ahead_kb: int = 0) -> torch.Tensor:
     """out = x @ w.T (+ bias | SwiGLU): x [M, K] bf16 with M <= 128, w [N, K] bf16 (the nn.Linear layout).
     Streams ``w`` once at HBM speed on tcgen05 tensor cores (TMA ring, TMEM accumulators, stream-K over one
     persistent CTA per SM, deterministic); capturable.  ``bias`` is added as a second bf16 rounding like the
     reference's separate ``qkv + bias`` (core/layer/model_graph.py:147).  ``swiglu``: ``w`` is the interleaved
     up/gate matrix of :func:`interleave_up_gate` and ``out [M, N/2] = silu(gate) * up`` with the rounding points
     of ``matmul`` -> ``swiglu_gemm`` (:183-184).  ``pdl``: programmatic dependent launch (the kernel before this
-    one in the stream must not write ``w`` / ``bias``)."""
+    one in the stream must not write ``w`` / ``bias``); ``l2_ahead_kb`` then also prefetches that much of every CTA's
+    weight share into L2 before the wait."""
     _req_cuda(x, w, out, bias)
     assert x.dim() == 2 and w.dim() == 2 and x.shape[1] == w.shape[1], "stream_gemm: x [M, K] @ w [N, K]^T"
     assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16, "stream_gemm: bf16 only"
@@ -480,11 +481,13 @@ def stream_gemm(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = 
         need = int(lib.b200_stream_gemm_workspace_bytes(M, N, int(grid)))
     ws = _workspace(x.device, need, "sgemm")
     epi = _lib.GEMM_EPI_SWIGLU if swiglu else (_lib.GEMM_EPI_BIAS if bias is not None else _lib.GEMM_EPI_NONE)
+    # with PDL: 16 KB weight boxes per CTA pulled into L2 before the wait on the previous kernel (l2_ahead_kb per CTA)
+    flags = (_lib.GEMM_FLAG_PDL | ((min(int(l2_ahead_kb) // 16, 0xffff)) << 8)) if pdl else 0
     check(lib.b200_stream_gemm(x.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None,
                                out.data_ptr(), ws.data_ptr(), ws.numel(), M, K, N,
                                x.stride(0) if M > 1 else max(x.stride(0), K), w.stride(0),
                                out.stride(0) if M > 1 else max(out.stride(0), n_out),
-                               epi, _lib.GEMM_FLAG_PDL if pdl else 0, int(grid), _stream()), "b200_stream_gemm")
+                               epi, flags, int(grid), _stream()), "b200_stream_gemm")
     return out
 
 

@@ -71,6 +71,9 @@ AR_MAX_WORLD, AR_MAX_CTAS, IPC_HANDLE_BYTES = 8, 1024, 64
 AR_MODE_ROW_SHARDED = 1
 AR_MODE_LL = 2
 AR_MODE_NVLS = 4
+AR_MODE_NVLS_ONEHOP = 8
+AR_FLAG_PDL = 0x100
+AR_FLAG_PDL = 0x100
 AR_NVLS_READY_WORD = AR_MAX_CTAS * (AR_MAX_WORLD + 1)
 AR_NVLS_DONE_WORD = AR_NVLS_READY_WORD + 32
 
@@ -121,6 +124,7 @@ SIGNATURES = {
     "b200_prefill_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200_paged_attn_prefill": (C.c_int, [C.POINTER(PrefillArgs), _vp]),
     "b200_debug_prefill_trace": (None, [_vp]),
+    "b200_debug_decode_trace": (None, [_vp]),
     "b200_allreduce_residual_rmsnorm": (C.c_int, [C.POINTER(ArArgs), _vp]),
     "b200_comm_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
     "b200_comm_free": (C.c_int, [_vp]),

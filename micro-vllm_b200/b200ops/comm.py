@@ -250,13 +250,16 @@ class PeerComm:
                                    weight: Optional[torch.Tensor], y: Optional[torch.Tensor],
                                    res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False,
                                    sharded: bool = False, trace: Optional[torch.Tensor] = None, ll: bool = False,
-                                   nvls: bool = False):
+                                   nvls: bool = False, pdl: bool = False, nvls1: bool = False):
         """res_out = bf16(bf16(sum over ranks of slot[slot_idx][:rows, :n]) + residual);
         y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable.
         ``sharded`` / ``nvls``: the row-sharded forms (B200_AR_MODE_ROW_SHARDED, B200_AR_MODE_NVLS) —
         ``y`` must be a prefix view of :meth:`ybuf`, and ``residual`` / ``res_out`` are only read /
-        written for the rows this rank owns.  ``ll``: the flag-in-data push form (same residual contract)."""
-        assert int(sharded) + int(ll) + int(nvls) <= 1, "PeerComm: choose one of sharded / ll / nvls"
+        written for the rows this rank owns.  ``ll``: the flag-in-data push form (same residual contract).
+        ``nvls1``: the one-hop NVLS form (B200_AR_MODE_NVLS_ONEHOP: the one-shot contract — replicated residual, any
+        local ``y``, alternate slots).  ``pdl``: launch with programmatic stream serialization (B200_AR_FLAG_PDL)."""
+        assert int(sharded) + int(ll) + int(nvls) + int(nvls1) <= 1, "PeerComm: choose one of sharded / ll / nvls / nvls1"
+        # "oneshot" here = no trailing barrier (peer-load one-shot and the one-hop NVLS form)
         mode = "sharded" if sharded else "ll" if ll else "nvls" if nvls else "oneshot"
         # The one-shot form has no trailing barrier: after a one-shot call on slot s, peers may still be READING
         # slot s, so the next call (of any form) must use the other slot.  The other forms end with a barrier.
@@ -288,6 +291,11 @@ class PeerComm:
             a.x_mc = self._mc_base + off
             a.y_mc = self._mc_base + yoff
             a.flags_mc = self._mc_base
+        if nvls1:
+            assert self.has_multicast, "PeerComm: the NVLS forms need a multicast mapping (symm back end on an NVSwitch node)"
+            a.mode = _lib.AR_MODE_NVLS_ONEHOP
+            a.x_mc = self._mc_base + off
+            a.flags_mc = self._mc_base
         if ll:
             # LL push form: flag-in-data packets through the staging areas; y is any local tensor
             assert y is not None
@@ -297,6 +305,8 @@ class PeerComm:
             for r in range(self.world):
                 a.xstage_peers[r] = self._peer_base[r] + self._xstage_off
                 a.ystage_peers[r] = self._peer_base[r] + self._ystage_off
+        if pdl:
+            a.mode |= _lib.AR_FLAG_PDL
         if trace is not None:
             assert trace.dtype == torch.int64 and trace.is_cuda and trace.numel() >= 4 * min(rows, _lib.AR_MAX_CTAS)
             a.trace = trace.data_ptr()

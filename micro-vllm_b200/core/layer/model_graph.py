@@ -74,7 +74,7 @@ class ModelGraphRunner:
         # The kernel launched right before a layer's attention is its QKV projection, which never
         # writes the lengths, the block table or cached pages, so programmatic dependent launch
         # would be legal here; measured on B200 it does not pay (profiles/r01), so it stays off.
-        self.use_pdl = 0
+        self.use_pdl = int(os.environ.get("B200_DECODE_PDL", "0"))      # 1 / 2: see B200_DECODE_FLAG_PDL(_LATE); A/B switch
         # Decode GEMMs: B200_SKINNY_GEMM = "auto" (default) sends a product through the
         # weight-streaming split-K kernel b200_skinny_gemm only where it was measured faster than cuBLAS on B200
         # (profiles/r01/skinny_gemm_*.json): deep-K, narrow-N products at <= 32 rows — down_proj, where cuBLAS
@@ -90,6 +90,11 @@ class ModelGraphRunner:
         self._stream_mode = os.environ.get("B200_STREAM_GEMM", "auto")
         self._stream = self._stream_mode != "0" and torch.device(device).type == "cuda"
         self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "0") == "1"
+        # With PDL a stream GEMM that follows a cross-GPU reduction (QKV, gate_up) also pulls this many KB of every
+        # CTA's weight share into L2 before it waits for the reduction (B200_GEMM_FLAG_L2_AHEAD); the reductions release
+        # their successor at their first instruction.  B200_AR_PDL = 1 launches the reductions themselves with PDL.
+        self._l2_ahead_kb = int(os.environ.get("B200_GEMM_L2_AHEAD_KB", "256")) if self.world_size > 1 else 0
+        self._ar_pdl = os.environ.get("B200_AR_PDL", "0") == "1"
         # TP only: while the NVLink reduction after o_proj / down_proj runs (a latency-bound kernel on a handful of SMs
         # that leaves HBM idle), a side stream asks L2 for the weights of the GEMMs behind it (b200_l2_prefetch), so the
         # reduction's latency is paid in parallel with weight bytes that have to come from HBM anyway.
@@ -173,7 +178,7 @@ class ModelGraphRunner:
         self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
         if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
             self._comm = None
-        # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls).  Default: "nvls" (in-switch reduction,
+        # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls | nvls1; nvls1 = one-hop in-switch form).  Default: "nvls" (in-switch reduction,
         # multimem.ld_reduce / multimem.st on the multicast mapping of the symmetric slabs) when the communicator has
         # a multicast range and the final norm can be fused; else "ll" from 4 ranks up; else "oneshot".  "nvls", "ll"
         # and "sharded" reduce + normalise each row on ONE owner rank and keep the residual stream row-sharded, so
@@ -186,9 +191,11 @@ class ModelGraphRunner:
             fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
             if want == "auto":
                 want = "nvls" if self._comm.has_multicast else ("ll" if self.world_size >= 4 else "oneshot")
-            if want == "nvls" and not self._comm.has_multicast:
+            if want in ("nvls", "nvls1") and not self._comm.has_multicast:
                 want = "ll" if self.world_size >= 4 else "oneshot"
             if want in ("ll", "sharded", "nvls") and fusable:
+                self._ar_mode = want
+            if want == "nvls1":                         # one-hop in-switch form: the one-shot contract, no ln_f condition
                 self._ar_mode = want
             if self._ar_mode in ("sharded", "nvls"):
                 self._normed = self._comm.ybuf(mb, self.hidden_dim)
@@ -219,7 +226,7 @@ class ModelGraphRunner:
         w_nk = getattr(block.attn, "_qkv_nk", None)
         if self._use_stream(bs, w_nk):
             return b200ops.stream_gemm(self._normed[:bs], w_nk, out=self._qkv[:bs], bias=block.attn._qkv_b,
-                                       pdl=self._stream_pdl)
+                                       pdl=self._stream_pdl, l2_ahead_kb=self._l2_ahead_kb)
         return self._mm(self._normed[:bs], block.attn._qkv_w, self._qkv[:bs], block.attn._qkv_b)
 
     def _flash_attn(self, qkv, block, layer_idx, bs, cache_manager, use_graph_cache, balanced=False):
@@ -246,7 +253,8 @@ class ModelGraphRunner:
         gu_nk, d_nk = getattr(block.mlp, "_gu_nk", None), getattr(block.mlp, "_d_nk", None)
         if self._use_stream(bs, gu_nk) and gu_nk.shape[0] % 16 == 0:
             # gate_up projection + SwiGLU in one launch (reference :183-184)
-            b200ops.stream_gemm(x_normed, gu_nk, out=self._swiglu_out[:bs], swiglu=True, pdl=self._stream_pdl)
+            b200ops.stream_gemm(x_normed, gu_nk, out=self._swiglu_out[:bs], swiglu=True, pdl=self._stream_pdl,
+                                l2_ahead_kb=self._l2_ahead_kb)
         else:
             self._mm(x_normed, block.mlp._gu, self._gate_up[:bs])
             swiglu_gemm(self._gate_up[:bs], self._swiglu_out[:bs])
@@ -308,7 +316,8 @@ class ModelGraphRunner:
             self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
                                                   y if norm is not None else None, res_out, eps, ss_rounded,
                                                   sharded=self._ar_mode == "sharded", ll=self._ar_mode == "ll",
-                                                  nvls=self._ar_mode == "nvls")
+                                                  nvls=self._ar_mode == "nvls", pdl=self._ar_pdl,
+                                                  nvls1=self._ar_mode == "nvls1")
         else:
             all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
             allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,
@@ -370,7 +379,9 @@ class ModelGraphRunner:
                 dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
                 with torch.no_grad():
                     for _ in range(3):
-                        self.decode(dummy, bs, cache_manager, use_graph_cache=False, balanced=balanced)
+                        lg = self.decode(dummy, bs, cache_manager, use_graph_cache=False, balanced=balanced)
+                        if greedy:                                   # the warm-up also reserves the arg-max scratch
+                            b200ops.greedy_argmax(lg, self._next_ids[:bs])
                 torch.cuda.synchronize()
                 g = torch.cuda.CUDAGraph()
                 with torch.no_grad(), torch.cuda.graph(g):
@@ -394,7 +405,9 @@ class ModelGraphRunner:
         """Which kernels run the four decode GEMMs (reported by the bench tools)."""
         if self._stream:
             which = "every decode GEMM" if self._stream_mode == "1" else "K >= 4N products (QKV of a TP shard), cuBLAS elsewhere"
-            return f"tcgen05 stream_gemm for {which}" + (" + PDL" if self._stream_pdl else "")
+            return (f"tcgen05 stream_gemm for {which}" +
+                    (f" + PDL (L2 ahead {self._l2_ahead_kb} KB/CTA behind reductions)" if self._stream_pdl else "") +
+                    (" + PDL reductions" if self._ar_pdl and self.world_size > 1 else ""))
         return f"cuBLAS (torch.matmul), B200_SKINNY_GEMM={self._skinny}"
 
     def forward(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:

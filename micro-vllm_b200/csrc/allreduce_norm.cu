@@ -20,6 +20,10 @@
 
 namespace b200 {
 
+#define B200_LAUNCH_AR(kernel, grid, threads, st, pdl, ...) do { \
+    cudaError_t le__ = launch_maybe_pdl(kernel, dim3(grid), dim3(threads), 0, st, pdl, __VA_ARGS__); \
+    if (le__ != cudaSuccess) { set_error("allreduce launch failed: %s", cudaGetErrorString(le__)); return (int)le__; } } while (0)
+
 struct ArParams {
     const __nv_bfloat16* x[B200_AR_MAX_WORLD];
     uint32_t* flags[B200_AR_MAX_WORLD];
@@ -40,6 +44,7 @@ struct ArParams {
     const __nv_bfloat16* x_mc;              // NVLS form: multicast address of the x slot (multimem.ld_reduce)
     __nv_bfloat16* y_mc;                    // NVLS form: multicast address of the y buffer (multimem.st)
     uint32_t* flags_mc;                     // NVLS form: multicast address of the flag region (multimem.red)
+    int pdl;                                // launched with programmatic stream serialization: wait for the previous kernel
 };
 
 __device__ __forceinline__ void stamp(const ArParams& p, int slot) {
@@ -122,6 +127,10 @@ allreduce_residual_rmsnorm_kernel(const __grid_constant__ ArParams p) {
     const int bid = blockIdx.x;
     const int T = blockDim.x;
     const int nvec = (int)(p.n >> 3);
+    // the kernel behind this one (a PDL-launched weight-streaming GEMM) may start fetching weights while this one
+    // sits in the cross-GPU exchange; its own griddepcontrol.wait still waits for this whole grid
+    pdl_release_next();
+    if (p.pdl) pdl_wait_prev();
     stamp(p, 0);
 
     if (TS) {
@@ -300,6 +309,10 @@ allreduce_ll_kernel(const __grid_constant__ ArParams p) {
     const int row = blockIdx.x;                              // grid = rows
     const int T = blockDim.x;
     const int nvec = (int)(p.n >> 3);
+    // the kernel behind this one (a PDL-launched weight-streaming GEMM) may start fetching weights while this one
+    // sits in the cross-GPU exchange; its own griddepcontrol.wait still waits for this whole grid
+    pdl_release_next();
+    if (p.pdl) pdl_wait_prev();
     stamp(p, 0);
     const uint32_t e = p.epoch[B200_AR_MAX_CTAS + 1] + 1u;   // one epoch per call, the same on every rank
     const int R = p.rows_per_rank;
@@ -465,12 +478,20 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     return v;
 }
 
-template <int VPT, typename WT>
+// ONE = the one-hop form: EVERY rank asks the switch for the sum of EVERY row (the switch reduces the same slot once
+// per requester — 1 MB per GPU at decode sizes, far below NVLink bandwidth), adds its REPLICATED residual, normalises
+// and stores y locally.  No second hop and no trailing barrier: like the one-shot peer-load form, consecutive calls
+// must alternate x slots, and res_out / residual are full tensors on every rank.
+template <int VPT, typename WT, bool ONE>
 __global__ void __launch_bounds__(1024)
 allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
     __shared__ float red[32];
     const int T = blockDim.x;
     const int nvec = (int)(p.n >> 3);
+    // the kernel behind this one (a PDL-launched weight-streaming GEMM) may start fetching weights while this one
+    // sits in the cross-GPU exchange; its own griddepcontrol.wait still waits for this whole grid
+    pdl_release_next();
+    if (p.pdl) pdl_wait_prev();
     stamp(p, 0);
     const uint32_t ready_t = p.epoch[B200_AR_EPOCH_NVLS_READY] + (uint32_t)world;
     const uint32_t done_t = p.epoch[B200_AR_EPOCH_NVLS_DONE] + (uint32_t)world * gridDim.x;
@@ -484,8 +505,8 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
     stamp(p, 1);
     // a CTA walks rows j, j + grid, ... of this rank's share: the grid is capped so that every CTA of the call is
     // resident at once (the done barrier below waits for ALL of them)
-    for (int64_t j = blockIdx.x; j < p.rows_per_rank; j += gridDim.x) {
-        const int64_t row = (int64_t)p.rank * p.rows_per_rank + j;
+    for (int64_t j = blockIdx.x; j < (ONE ? p.rows : (int64_t)p.rows_per_rank); j += gridDim.x) {
+        const int64_t row = ONE ? j : (int64_t)p.rank * p.rows_per_rank + j;
         if (row >= p.rows) break;
         const bool has_r = p.r != nullptr;
         float ss = 0.0f;
@@ -544,19 +565,22 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
-                multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);      // lands in every rank's y buffer
+                if constexpr (ONE) st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
+                else multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);  // lands in every rank's y buffer
             }
         }
     }
     stamp(p, 2);
     __syncthreads();                                         // every thread's multimem.st is ordered before the release below
     if (threadIdx.x == 0) {
-        multimem_red_add_release(p.flags_mc + B200_AR_NVLS_DONE_WORD, 1u);
-        // all CTAs of all ranks have stored their rows (and finished reading x)
-        if ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
-            const long long t0 = now_ns();
-            while ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
-                if (now_ns() - t0 > p.timeout_ns) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+        if constexpr (!ONE) {
+            multimem_red_add_release(p.flags_mc + B200_AR_NVLS_DONE_WORD, 1u);
+            // all CTAs of all ranks have stored their rows (and finished reading x)
+            if ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
+                const long long t0 = now_ns();
+                while ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
+                    if (now_ns() - t0 > p.timeout_ns) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+                }
             }
         }
         // the last CTA of the call advances the targets (every CTA read them before it could arrive here)
@@ -564,22 +588,23 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
         if (arrived == gridDim.x - 1) {
             p.epoch[B200_AR_EPOCH_NVLS_ARRIVE] = 0u;
             p.epoch[B200_AR_EPOCH_NVLS_READY] = ready_t;
-            p.epoch[B200_AR_EPOCH_NVLS_DONE] = done_t;
+            if constexpr (!ONE) p.epoch[B200_AR_EPOCH_NVLS_DONE] = done_t;
         }
     }
     stamp(p, 3);
 }
 
-template <typename WT>
+template <typename WT, bool ONE>
 static int launch_nvls(const ArParams& p, int world, cudaStream_t st) {
     const int64_t nvec = p.n / 8;
-    const unsigned grid = (unsigned)(p.rows_per_rank < 128 ? p.rows_per_rank : 128);   // all resident at once (148 SMs)
+    const int64_t my_rows = ONE ? p.rows : (int64_t)p.rows_per_rank;
+    const unsigned grid = (unsigned)(my_rows < 128 ? my_rows : 128);   // all resident at once (148 SMs)
     if (nvec <= 1024) {
         int threads = (int)((nvec + 31) & ~31LL);
-        allreduce_nvls_kernel<1, WT><<<grid, threads, 0, st>>>(p, world);
+        B200_LAUNCH_AR((allreduce_nvls_kernel<1, WT, ONE>), grid, threads, st, p.pdl != 0, p, world);
     } else {
         int threads = (int)((((nvec + 1) / 2) + 31) & ~31LL);
-        allreduce_nvls_kernel<2, WT><<<grid, threads, 0, st>>>(p, world);
+        B200_LAUNCH_AR((allreduce_nvls_kernel<2, WT, ONE>), grid, threads, st, p.pdl != 0, p, world);
     }
     B200_CHECK_LAUNCH();
     return 0;
@@ -591,13 +616,13 @@ static int launch_ll(const ArParams& p, cudaStream_t st) {
     const unsigned grid = (unsigned)p.rows;
     if (nvec <= 512) {
         const int threads = (int)((nvec + 31) & ~31LL);
-        allreduce_ll_kernel<WS, 1, WT><<<grid, threads, 0, st>>>(p);
+        B200_LAUNCH_AR((allreduce_ll_kernel<WS, 1, WT>), grid, threads, st, p.pdl != 0, p);
     } else if (nvec <= 1024) {
         const int threads = (int)(((nvec + 1) / 2 + 31) & ~31LL);
-        allreduce_ll_kernel<WS, 2, WT><<<grid, threads, 0, st>>>(p);
+        B200_LAUNCH_AR((allreduce_ll_kernel<WS, 2, WT>), grid, threads, st, p.pdl != 0, p);
     } else {
         const int threads = (int)(((nvec + 3) / 4 + 31) & ~31LL);
-        allreduce_ll_kernel<WS, 4, WT><<<grid, threads, 0, st>>>(p);
+        B200_LAUNCH_AR((allreduce_ll_kernel<WS, 4, WT>), grid, threads, st, p.pdl != 0, p);
     }
     B200_CHECK_LAUNCH();
     return 0;
@@ -620,11 +645,11 @@ static int launch_ar(const ArParams& p, cudaStream_t st) {
     if (nvec <= 1024) {
         int threads = (int)((nvec + 31) & ~31LL);
         if (threads < 32 * ((WS + 31) / 32)) threads = 32;
-        allreduce_residual_rmsnorm_kernel<WS, 1, WT, TS><<<grid, threads, 0, st>>>(p);
+        B200_LAUNCH_AR((allreduce_residual_rmsnorm_kernel<WS, 1, WT, TS>), grid, threads, st, p.pdl != 0, p);
     } else {
         int threads = (int)((nvec + 1) / 2);
         threads = (threads + 31) & ~31;
-        allreduce_residual_rmsnorm_kernel<WS, 2, WT, TS><<<grid, threads, 0, st>>>(p);
+        B200_LAUNCH_AR((allreduce_residual_rmsnorm_kernel<WS, 2, WT, TS>), grid, threads, st, p.pdl != 0, p);
     }
     B200_CHECK_LAUNCH();
     return 0;
@@ -711,12 +736,14 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         p.rows_per_rank = (int)((a->rows + a->world - 1) / a->world);
         if (p.rows_per_rank < 1) p.rows_per_rank = 1;
     }
-    const bool nvls = (a->mode & B200_AR_MODE_NVLS) != 0;
+    const bool nvls1 = (a->mode & B200_AR_MODE_NVLS_ONEHOP) != 0;
+    const bool nvls = (a->mode & B200_AR_MODE_NVLS) != 0 || nvls1;
     if (nvls) {
         if (sharded || ll) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: choose one of ROW_SHARDED / LL / NVLS");
         if (a->world < 2) B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: NVLS form needs world > 1");
         if (!a->weight) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the norm (weight, y)");
-        if (!a->x_mc || !a->y_mc || !a->flags_mc || !aligned16(a->x_mc) || !aligned16(a->y_mc))
+        if (nvls1 && (a->mode & B200_AR_MODE_NVLS)) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: choose one of NVLS / NVLS_ONEHOP");
+        if (!a->x_mc || !a->flags_mc || !aligned16(a->x_mc) || (!nvls1 && (!a->y_mc || !aligned16(a->y_mc))))
             B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the multicast addresses of x, y and the flags");
         if (a->rows > 65535LL * a->world) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: NVLS form: too many rows");
         p.x_mc = (const __nv_bfloat16*)a->x_mc;
@@ -737,10 +764,16 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
     const int ms = a->timeout_ms > 0 ? a->timeout_ms : 2000;
     p.timeout_ns = (long long)ms * 1000000LL;
     p.trace = (unsigned long long*)a->trace;
+    p.pdl = (a->mode & B200_AR_FLAG_PDL) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
+    if (nvls1) {
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, true>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, true>(p, a->world, st);
+        B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
+    }
     if (nvls) {
-        if (a->w_dtype == B200_DT_F32) return launch_nvls<float>(p, a->world, st);
-        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16>(p, a->world, st);
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, false>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, false>(p, a->world, st);
         B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
     }
     if (ll) {

@@ -17,6 +17,23 @@ void set_error(const char* fmt, ...);
 #define B200_CHECK_LAUNCH() do { cudaError_t e__ = cudaGetLastError(); \
     if (e__ != cudaSuccess) { ::b200::set_error("launch failed: %s", cudaGetErrorString(e__)); return (int)e__; } } while (0)
 
+// Kernel launch with (optionally) programmatic stream serialization: the kernel may begin while the previous kernel of
+// the stream is still running and must execute griddepcontrol.wait before it touches anything that kernel produces.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_maybe_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                           bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+__device__ __forceinline__ void pdl_release_next() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait_prev() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // ---------------------------------------------------------------- bf16 packing

@@ -59,10 +59,22 @@ struct DecodeParams {
     int n_blocks, block_size, max_blocks_per_seq;
     int page_shift;                      // log2(block_size) or -1 when block_size is not a power of two
     int pdl;                             // launched with programmatic stream serialization
+    unsigned long long* trace;           // debug only (b200_debug_decode_trace): [CTA][8] %globaltimer stamps
     int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, o_sb, o_sh;
     int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
     float scale, scale_log2;
 };
+
+// Timeline of every CTA of the split-KV grid (debug): 0 entry, 1 first loads issued, 2 prologue done (q rotated, new
+// token staged), 3 first stage landed, 4 streaming loop done, 5 partial written, 6 exit
+__device__ __forceinline__ void dec_stamp(const DecodeParams& p, int ev) {
+    if (p.trace != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const size_t cta = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        p.trace[cta * 8 + ev] = t;
+    }
+}
 
 template <int D_, int NWARPS_, int TPS_, int STAGES_, int MINB_>
 struct DCfg {
@@ -169,6 +181,7 @@ __device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* sme
     // cache_seqlens and the block table.
 #pragma unroll
     for (int i = 0; i < STAGES - 1; ++i) issue(i);
+    dec_stamp(p, 1);
 
     // Programmatic dependent launch: everything above only read state that the caller
     // guarantees is older than the preceding kernel in the stream (lengths, block table, cached
@@ -210,6 +223,7 @@ __device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* sme
         }
     }
     __syncthreads();
+    dec_stamp(p, 2);
 
     // ---- append: rotated k_new / raw v_new -> page block_table[b, pos / bs], slot pos % bs
     if (owns_new && grp == 0 && tid < 2 * CPR) {
@@ -254,6 +268,7 @@ __device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* sme
             issue(i + STAGES - 1);
             cp_async_wait<STAGES - 1>();
             __syncwarp();
+            if (i == 0) dec_stamp(p, 3);
             const int t0 = (c0 + i) * C::CH + warp * TPS;
             if (t0 >= seqlen_k) continue;                            // warp-uniform
             const uint32_t kt = my_kv_u32 + (i % STAGES) * C::STAGE_B;
@@ -349,6 +364,7 @@ __device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* sme
         l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     }
     cp_async_wait<0>();
+    dec_stamp(p, 4);
     // late trigger: the next kernel's CTAs may take over SMs from here on (their KV prefetch
     // overlaps this kernel's merge epilogue and tail)
     if (pdl && p.pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -407,6 +423,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     const int g0 = pc.grp * p.gpg;
     const int gcount = min(p.gpg, p.G - g0);
     const int hq0 = pc.kvh * p.G + g0;
+    dec_stamp(p, 0);
     pc.pos = __ldg(p.seqlens + b);
     pc.seqlen_k = pc.pos + (p.k_new != nullptr ? 1 : 0);
     pc.n_chunks = (pc.seqlen_k + C::CH - 1) / C::CH;
@@ -424,6 +441,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
             if (d == 0) p.ws_lse[(bh0 + g) * S + split] = lse;
         }
     });
+    dec_stamp(p, 5);
     if (S == 1) return;
 
     // ---- split merge by the last-arriving CTA of this (b, kv head, group)
@@ -439,7 +457,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
         *s_flag = last;
     }
     __syncthreads();
-    if (!*s_flag) return;
+    if (!*s_flag) { dec_stamp(p, 6); return; }
 
     float* c_w = reinterpret_cast<float*>(smem);        // [gcount][S] merge weights
     for (int idx = tid; idx < gcount * S; idx += C::THREADS) {
@@ -472,6 +490,7 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
         }
         p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(acc);
     }
+    dec_stamp(p, 7);                                    // the merging CTA of the segment
 }
 
 // ------------------------------------------------------------------ balanced persistent form
@@ -730,6 +749,10 @@ static int launch_decode(const DecodeParams& p, int S, cudaStream_t st) {
 
 using namespace b200;
 
+static unsigned long long* g_dec_trace = nullptr;
+// Debug only: uint64 [CTAs][8] device buffer that the NEXT split-KV launches stamp with %globaltimer (NULL = off).
+extern "C" void b200_debug_decode_trace(void* dev_ptr) { g_dec_trace = (unsigned long long*)dev_ptr; }
+
 extern "C" int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D, int32_t num_splits) {
     if (B <= 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || num_splits <= 0 || Hq % Hkv != 0) return -1;
     return ws_layout(B, Hq, D, num_splits).total;
@@ -807,6 +830,7 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     p.n_blocks = a->n_blocks; p.block_size = a->block_size; p.max_blocks_per_seq = a->max_blocks_per_seq;
     p.page_shift = -1;
     for (int sft = 5; sft < 31; ++sft) if ((1 << sft) == a->block_size) p.page_shift = sft;
+    p.trace = balanced ? nullptr : g_dec_trace;
     p.pdl = (a->flags & B200_DECODE_FLAG_PDL) ? ((a->flags & B200_DECODE_FLAG_PDL_LATE) ? 2 : 1) : 0;
     p.q_sb = a->q_stride_b; p.q_sh = a->q_stride_h; p.k_sb = a->k_stride_b; p.k_sh = a->k_stride_h;
     p.v_sb = a->v_stride_b; p.v_sh = a->v_stride_h; p.o_sb = a->o_stride_b; p.o_sh = a->o_stride_h;

@@ -45,6 +45,10 @@ __device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap
                  " [%0], [%1, {%3, %4}], [%2], %5;"
                  :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
 }
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+                 :: "l"(map), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
                  "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -77,6 +81,7 @@ struct SgParams {
     int n_tiles, kblocks;            // 128-row weight tiles, 64-element k-blocks
     long long units;                 // n_tiles * kblocks
     int epilogue, flags;
+    int l2_ahead;                    // PDL form: weight boxes (16 KB) per CTA prefetched into L2 before the dependency wait
     unsigned long long* trace;       // debug only (b200_debug_stream_gemm_trace): [grid][8] %globaltimer stamps
 };
 
@@ -174,6 +179,13 @@ stream_gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
                 for (int j = 0; j < pre; ++j) {
                     mbar_expect_tx(full_bar(j), C::STAGE_BYTES);
                     tma_load_2d_hint(base + j * C::STAGE_BYTES, &tm_w, full_bar(j), k2 * 64, t2 * 128, pol_w);
+                    if (++k2 == KB) { k2 = 0; ++t2; }
+                }
+                // ... and the next boxes of this CTA's share are pulled into L2 (no shared memory needed): while the
+                // kernel before this one sits in a cross-GPU reduction, HBM streams the weights it is about to need
+                const int ahead = n_units - pre < (int)p.l2_ahead ? n_units - pre : (int)p.l2_ahead;
+                for (int j = 0; j < ahead; ++j) {
+                    tma_prefetch_l2_2d(&tm_w, k2 * 64, t2 * 128);
                     if (++k2 == KB) { k2 = 0; ++t2; }
                 }
                 griddep_wait();                                   // ... x (and the workspace) are only touched below this line
@@ -517,7 +529,8 @@ extern "C" int b200_stream_gemm(const void* x, const void* w, const void* bias, 
     p.n_tiles = (int)((N + 127) / 128);
     p.kblocks = (int)(K / 64);
     p.units = (long long)p.n_tiles * p.kblocks;
-    p.epilogue = epilogue; p.flags = flags;
+    p.epilogue = epilogue; p.flags = flags & 0xff;
+    p.l2_ahead = (flags >> 8) & 0xffff;
     p.trace = g_sg_trace;
     const int grid = sg_grid(p.units, grid_hint);
     const int NB = sg_pad_rows(M);

@@ -112,14 +112,14 @@ def test_stream_gemm_graph_replay_pdl_and_errors():
     w2 = (torch.randn(K, N, device="cuda") * 0.05).to(torch.bfloat16)
     mid = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
     out = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
-    for pdl in (False, True):
-        b200ops.stream_gemm(x, w, out=mid, pdl=pdl)
-        b200ops.stream_gemm(mid, w2, out=out, pdl=pdl)
+    for pdl, ahead in ((False, 0), (True, 0), (True, 64), (True, 4096)):     # 4096 KB/CTA: beyond every CTA's share
+        b200ops.stream_gemm(x, w, out=mid, pdl=pdl, l2_ahead_kb=ahead)
+        b200ops.stream_gemm(mid, w2, out=out, pdl=pdl, l2_ahead_kb=ahead)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            b200ops.stream_gemm(x, w, out=mid, pdl=pdl)               # a chain: the second product consumes the first
-            b200ops.stream_gemm(mid, w2, out=out, pdl=pdl)
+            b200ops.stream_gemm(x, w, out=mid, pdl=pdl, l2_ahead_kb=ahead)   # a chain: the second product consumes the first
+            b200ops.stream_gemm(mid, w2, out=out, pdl=pdl, l2_ahead_kb=ahead)
         for _ in range(3):
             x.copy_(torch.randn(M, K, device="cuda").to(torch.bfloat16))
             mid.zero_()
