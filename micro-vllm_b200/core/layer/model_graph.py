@@ -190,7 +190,13 @@ class ModelGraphRunner:
             want = os.environ.get("B200_AR_MODE", "auto")
             fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
             if want == "auto":
-                want = "nvls" if self._comm.has_multicast else ("ll" if self.world_size >= 4 else "oneshot")
+                # measured (profiles/r02/allreduce_tp*.json): at 2 ranks the peer-load one-shot form wins (7 us; one peer
+                # to read); from 4 ranks up the one-hop in-switch form costs the same one switch round trip whatever the
+                # world size, the peer-load form grows with world - 1
+                if self.world_size >= 4:
+                    want = "nvls1" if self._comm.has_multicast else "ll"
+                else:
+                    want = "oneshot"
             if want in ("nvls", "nvls1") and not self._comm.has_multicast:
                 want = "ll" if self.world_size >= 4 else "oneshot"
             if want in ("ll", "sharded", "nvls") and fusable:

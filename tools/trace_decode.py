@@ -42,7 +42,8 @@ def main():
     q = torch.randn(B, Hq, D, device=dev).to(torch.bfloat16)
     k = torch.randn(B, Hkv, D, device=dev).to(torch.bfloat16)
     v = torch.randn(B, Hkv, D, device=dev).to(torch.bfloat16)
-    cos, sin = build_rotary_tables(D, ctx + 16, 10000.0, dev)
+    cos, sin = build_rotary_tables(D, ctx + 16)
+    cos, sin = cos[:, : D // 2].contiguous().to(dev), sin[:, : D // 2].contiguous().to(dev)
     S = a.splits or b200ops.decode_num_splits(B, Hkv, per_seq * page, b200ops.sm_count(dev))
     out = torch.empty_like(q)
 
