@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 14
+#define B200_ABI_VERSION 15
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -467,6 +467,33 @@ typedef struct b200_ar_args {
 #define B200_AR_MODE_NVLS_ONEHOP 8
 
 int b200_allreduce_residual_rmsnorm(const b200_ar_args* args, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Column all-gather over peer memory — the collective of a VOCAB-PARALLEL lm_head.  The reference keeps lm_head
+ * replicated under tensor parallelism (/root/reference/models/adapter.py:25, core/layer/model_graph.py:223): every
+ * rank streams the whole [vocab, hidden] matrix.  With this call every rank multiplies by its vocab / world rows and
+ * the [rows, vocab] logits are assembled on EVERY rank: rank r's block src [rows, cols_local] lands at columns
+ * [r * cols_local, (r + 1) * cols_local) of every rank's dst (one multimem.st per 16 bytes when dst_mc / flags_mc are
+ * given, else `world` peer stores).  The call returns on a rank (stream order) only after every rank's block has
+ * landed in that rank's dst.  flag_peers / epoch: the regions of b200_ar_args (one more counter word each).
+ * Caller's duty (WAR): a rank's dst may only be overwritten after that rank consumed it; any barrier-carrying
+ * collective between two gathers that every rank enters after its consumer kernels (the decode step's reductions)
+ * provides that.  flags: bit 0 = launch with programmatic stream serialization.
+ * ------------------------------------------------------------------------ */
+typedef struct b200_gather_args {
+    const void* src;                          /* local bf16 [rows, cols_local]                                 */
+    void*       dst_peers[B200_AR_MAX_WORLD]; /* rank r's gather buffer bf16 [rows, world * cols_local]        */
+    void*       dst_mc;                       /* multicast address of the gather buffer, or NULL               */
+    void*       flag_peers[B200_AR_MAX_WORLD];/* rank r's flag region (as in b200_ar_args)                     */
+    void*       flags_mc;                     /* multicast address of the flag region, or NULL (with dst_mc)   */
+    void*       epoch;                        /* local epoch words (as in b200_ar_args; needs MAX_CTAS + 10)   */
+    int64_t rows, cols_local;
+    int64_t stride_src, stride_dst;           /* elements                                                      */
+    int32_t rank, world;
+    int32_t timeout_ms;                       /* 0 = default 2000                                              */
+    int32_t flags;
+} b200_gather_args;
+int b200_allgather_cols(const b200_gather_args* args, void* stream);
 
 /* Peer-memory plumbing (init time only; these DO allocate / synchronise).
  * b200_comm_alloc: cudaMalloc + zero fill of an IPC-exportable buffer on the current device.

@@ -180,6 +180,20 @@ def decode_algorithmic_bytes(seqlens_after, Hq: int, Hkv: int, D: int, block_siz
 
 
 _BALANCED_ENV = None
+_TUNE: dict = {}
+
+
+def _tune(name: str) -> int:
+    """Integer tuning override from the environment (read once); 0 = unset."""
+    v = _TUNE.get(name)
+    if v is None:
+        import os
+        try:
+            v = int(os.environ.get(name, "0"))
+        except ValueError:
+            v = 0
+        _TUNE[name] = v
+    return v
 
 
 def decode_use_balanced(batch: int, kv_heads: int, n_sm: int = 148) -> bool:
@@ -304,6 +318,10 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     if num_splits <= 0:
         num_splits = 1 if balanced else decode_num_splits(B, Hkv, block_table.shape[1] * block_size,
                                                           sm_count(q.device))
+        if not balanced and _tune("B200_DECODE_SPLITS") > 0:          # tuning override (A/B runs), launch-time constant
+            num_splits = _tune("B200_DECODE_SPLITS")
+    if variant == 0 and _tune("B200_DECODE_VARIANT") > 0:
+        variant = _tune("B200_DECODE_VARIANT")
     a.num_splits, a.variant = int(num_splits), int(variant)
     a.flags = 0 if not pdl else (_lib.DECODE_FLAG_PDL | (_lib.DECODE_FLAG_PDL_LATE if int(pdl) == 2 else 0))
     if balanced:

@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 
 class DecodeArgs(C.Structure):
@@ -93,6 +93,16 @@ class ArArgs(C.Structure):
     ]
 
 
+class GatherArgs(C.Structure):
+    """struct b200_gather_args (include/b200_abi.h)."""
+    _fields_ = [
+        ("src", _vp), ("dst_peers", _vp * AR_MAX_WORLD), ("dst_mc", _vp),
+        ("flag_peers", _vp * AR_MAX_WORLD), ("flags_mc", _vp), ("epoch", _vp),
+        ("rows", _i64), ("cols_local", _i64), ("stride_src", _i64), ("stride_dst", _i64),
+        ("rank", _i32), ("world", _i32), ("timeout_ms", _i32), ("flags", _i32),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200_abi.h declares
 SIGNATURES = {
     "b200_version": (C.c_int, []),
@@ -126,6 +136,7 @@ SIGNATURES = {
     "b200_debug_prefill_trace": (None, [_vp]),
     "b200_debug_decode_trace": (None, [_vp]),
     "b200_allreduce_residual_rmsnorm": (C.c_int, [C.POINTER(ArArgs), _vp]),
+    "b200_allgather_cols": (C.c_int, [C.POINTER(GatherArgs), _vp]),
     "b200_comm_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
     "b200_comm_free": (C.c_int, [_vp]),
     "b200_ipc_export": (C.c_int, [_vp, _vp]),

@@ -7,7 +7,7 @@ elementwise kernels that follow it at core/layer/model_graph.py:210-216 and :219
 One process per GPU.  Every rank owns ONE symmetric slab, laid out as
 
     [ flags u32[1024][8] + u32[1024] + NVLS counters | epoch u32[1032] (local only) | pad | slot 0 |
-      slot 1 | y | x staging (LL) | y staging (LL) ]
+      slot 1 | y | x staging (LL) | y staging (LL) | gather buffer (optional) ]
 
 and maps every peer's slab.  Two plumbing back ends provide the slab (``B200_COMM_BACKEND`` =
 ``auto`` | ``symm`` | ``ipc``):
@@ -35,12 +35,12 @@ from typing import List, Optional
 import torch
 
 from . import _lib
-from ._lib import ArArgs, check, lib
+from ._lib import ArArgs, GatherArgs, check, lib
 
 # ready flags [1024][8] + done flags [1024] + the two NVLS counters (128 bytes apart)
 _FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4 + 256
 # per-CTA epochs, error word, LL call + arrival counters, NVLS targets + arrival counter
-_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 8) * 4 + 255) // 256 * 256
+_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 16) * 4 + 255) // 256 * 256
 _HEADER = _FLAG_BYTES + _EPOCH_BYTES
 _ERR_OFF = _FLAG_BYTES + _lib.AR_MAX_CTAS * 4
 
@@ -104,7 +104,7 @@ class PeerComm:
     """Two symmetric bf16 slots of ``slot_bytes`` each on every rank of ``group`` + flag arrays."""
 
     def __init__(self, slot_bytes: int, group=None, device: Optional[torch.device] = None, timeout_ms: int = 2000,
-                 backend: Optional[str] = None):
+                 backend: Optional[str] = None, gather_bytes: int = 0):
         import torch.distributed as dist
         assert dist.is_initialized(), "PeerComm needs torch.distributed (one process per GPU)"
         self.group = group if group is not None else dist.group.WORLD
@@ -118,7 +118,10 @@ class PeerComm:
         self._xstage_off = _HEADER + 3 * self.slot_bytes
         self._xstage_bytes = 2 * self.slot_bytes + self.world * 16384 * 4
         self._ystage_off = self._xstage_off + self._xstage_bytes
-        total = self._ystage_off + 2 * self.slot_bytes
+        # optional gather buffer (vocab-parallel lm_head: [rows, vocab] logits assembled on every rank)
+        self._gather_off = self._ystage_off + 2 * self.slot_bytes
+        self.gather_bytes = (int(gather_bytes) + 255) // 256 * 256
+        total = self._gather_off + self.gather_bytes
         self._total = total
         self._imported: List[int] = []
         self._symm = None
@@ -219,6 +222,37 @@ class PeerComm:
         assert rows * n * 2 <= self.slot_bytes, "PeerComm y buffer too small"
         off = _HEADER + 2 * self.slot_bytes
         return self._bytes[off: off + rows * n * 2].view(torch.bfloat16).view(rows, n)
+
+    def gather_buf(self, rows: int, cols: int) -> torch.Tensor:
+        """bf16 [rows, cols] view of the local gather buffer (:meth:`allgather_cols` fills it on every rank)."""
+        assert rows * cols * 2 <= self.gather_bytes, "PeerComm gather buffer too small"
+        return self._bytes[self._gather_off: self._gather_off + rows * cols * 2].view(torch.bfloat16).view(rows, cols)
+
+    def allgather_cols(self, src: torch.Tensor, dst: torch.Tensor, pdl: bool = False) -> torch.Tensor:
+        """``dst[:, r * c:(r + 1) * c] = src of rank r`` on EVERY rank (``b200_allgather_cols``): ``src`` bf16
+        ``[rows, c]`` local, ``dst`` a ``[rows, world * c]`` prefix view of :meth:`gather_buf`.  Current stream;
+        capturable; complete on this rank when the kernel ends.  Between two calls every rank must pass another
+        barrier-carrying collective after its consumers of ``dst`` (the decode step's reductions do)."""
+        assert src.is_cuda and src.dtype == torch.bfloat16 and src.dim() == 2 and src.stride(1) == 1
+        rows, c = src.shape
+        assert dst.shape == (rows, self.world * c) and dst.stride(1) == 1
+        off = dst.data_ptr() - self._base
+        assert self._gather_off <= off and off + (rows - 1) * dst.stride(0) * 2 + self.world * c * 2 <= self._gather_off + self.gather_bytes, \
+            "PeerComm.allgather_cols: dst must live in gather_buf()"
+        a = GatherArgs()
+        a.src = src.data_ptr()
+        for r in range(self.world):
+            a.dst_peers[r] = self._peer_base[r] + off
+            a.flag_peers[r] = self._peer_base[r]
+        if self.has_multicast:
+            a.dst_mc = self._mc_base + off
+            a.flags_mc = self._mc_base
+        a.epoch = self._base + _FLAG_BYTES
+        a.rows, a.cols_local = rows, c
+        a.stride_src, a.stride_dst = src.stride(0) if rows > 1 else max(src.stride(0), c), dst.stride(0) if rows > 1 else max(dst.stride(0), self.world * c)
+        a.rank, a.world, a.timeout_ms, a.flags = self.rank, self.world, self.timeout_ms, 1 if pdl else 0
+        check(lib.b200_allgather_cols(C.byref(a), torch.cuda.current_stream().cuda_stream), "b200_allgather_cols")
+        return dst
 
     def fits(self, rows: int, n: int) -> bool:
         return rows * n * 2 <= self.slot_bytes and n % 8 == 0 and n <= 16384

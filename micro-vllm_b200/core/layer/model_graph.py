@@ -89,7 +89,7 @@ class ModelGraphRunner:
         # dependent launch (weight boxes requested before the previous kernel has drained).
         self._stream_mode = os.environ.get("B200_STREAM_GEMM", "auto")
         self._stream = self._stream_mode != "0" and torch.device(device).type == "cuda"
-        self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "0") == "1"
+        self._stream_pdl = os.environ.get("B200_STREAM_GEMM_PDL", "1") == "1"
         # With PDL a stream GEMM that follows a cross-GPU reduction (QKV, gate_up) also pulls this many KB of every
         # CTA's weight share into L2 before it waits for the reduction (B200_GEMM_FLAG_L2_AHEAD); the reductions release
         # their successor at their first instruction.  B200_AR_PDL = 1 launches the reductions themselves with PDL.
@@ -98,8 +98,10 @@ class ModelGraphRunner:
         # TP only: while the NVLink reduction after o_proj / down_proj runs (a latency-bound kernel on a handful of SMs
         # that leaves HBM idle), a side stream asks L2 for the weights of the GEMMs behind it (b200_l2_prefetch), so the
         # reduction's latency is paid in parallel with weight bytes that have to come from HBM anyway.
-        # B200_AR_PREFETCH_MB = how many MB per reduction (0 = off).
-        self._prefetch_bytes = int(float(os.environ.get("B200_AR_PREFETCH_MB", "48")) * 1e6) if self.world_size > 1 else 0
+        # B200_AR_PREFETCH_MB = how many MB per reduction (0 = off, the default: measured on 8 B200s the side-stream
+        # launches cost more than the prefetch saves, 2.79 vs 2.72 ms per step; the PDL form of the stream GEMM does
+        # the same job from inside the kernel that needs the weights).
+        self._prefetch_bytes = int(float(os.environ.get("B200_AR_PREFETCH_MB", "0")) * 1e6) if self.world_size > 1 else 0
         self._side_stream = None
         self.attention = PagedAttention(num_heads, head_size, kv_num_heads, device, max_batch_size,
                                         max_blocks=max_blocks, rotary_interleaved=False)
@@ -175,9 +177,26 @@ class ModelGraphRunner:
         self._mlp_out = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
         self._h = torch.empty((mb, self.hidden_dim), dtype=dt, device=dev)
         # TP: the two GEMMs whose outputs are summed over ranks write into peer-visible slots
-        self._comm = peer_comm(mb * self.hidden_dim * 2) if self.world_size > 1 else None
+        # Vocab-parallel lm_head (B200_HEAD_SHARD, default on under TP): the reference keeps lm_head replicated
+        # (models/adapter.py:25) — at TP = 8 on the 70B shape that is 2.1 GB streamed per step on every rank, 13 % of
+        # the step.  Here rank r multiplies by rows [r V/ws, (r+1) V/ws) of the SAME weight and the logits are
+        # assembled on every rank by b200_allgather_cols (peer stores / multimem.st): same [B, vocab] result.
+        head = getattr(self.model, "lm_head", None)
+        hw = getattr(head, "weight", None)
+        shard_head = (self.world_size > 1 and os.environ.get("B200_HEAD_SHARD", "1") != "0" and hw is not None
+                      and getattr(head, "bias", None) is None and hw.dim() == 2 and hw.is_contiguous()
+                      and hw.shape[0] == self.vocab_size and self.vocab_size % (8 * self.world_size) == 0
+                      and hw.dtype == torch.bfloat16)
+        gather_bytes = mb * self.vocab_size * 2 if shard_head else 0
+        self._comm = peer_comm(mb * self.hidden_dim * 2, gather_bytes) if self.world_size > 1 else None
         if self._comm is not None and not self._comm.fits(mb, self.hidden_dim):
             self._comm = None
+        self._head_w = None
+        if shard_head and self._comm is not None and self._comm.gather_bytes >= gather_bytes:
+            vs = self.vocab_size // self.world_size
+            self._head_w = hw.data[self.rank * vs:(self.rank + 1) * vs]          # a view: rows of the replicated matrix
+            self._logits_local = torch.empty((mb, vs), dtype=dt, device=dev)
+            self._logits = self._comm.gather_buf(mb, self.vocab_size)
         # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls | nvls1; nvls1 = one-hop in-switch form).  Default: "nvls" (in-switch reduction,
         # multimem.ld_reduce / multimem.st on the multicast mapping of the symmetric slabs) when the communicator has
         # a multicast range and the final norm can be fused; else "ll" from 4 ranks up; else "oneshot".  "nvls", "ll"
@@ -190,11 +209,12 @@ class ModelGraphRunner:
             want = os.environ.get("B200_AR_MODE", "auto")
             fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
             if want == "auto":
-                # measured (profiles/r02/allreduce_tp*.json): at 2 ranks the peer-load one-shot form wins (7 us; one peer
-                # to read); from 4 ranks up the one-hop in-switch form costs the same one switch round trip whatever the
-                # world size, the peer-load form grows with world - 1
+                # measured (profiles/r02/allreduce_tp{2,8}.json, 64 x 8192 bf16): 2 ranks — peer-load one-shot 7.0 us,
+                # one-hop NVLS 9.2, two-hop NVLS 13.4, NCCL 19.1; 8 ranks — two-hop NVLS 13.5 us, one-hop NVLS 18.0 (every
+                # rank pulls the whole tensor through the switch: 8 MB leave each GPU), one-shot 21.7, LL 33.5, NCCL 34.1.
+                # Whole L70-shaped step at TP = 8: 2.56 / 2.72 / 2.84 / 3.20 ms (nvls / nvls1 / oneshot / ll).
                 if self.world_size >= 4:
-                    want = "nvls1" if self._comm.has_multicast else "ll"
+                    want = ("nvls" if fusable else "nvls1") if self._comm.has_multicast else "ll"
                 else:
                     want = "oneshot"
             if want in ("nvls", "nvls1") and not self._comm.has_multicast:
@@ -268,8 +288,18 @@ class ModelGraphRunner:
             return b200ops.stream_gemm(self._swiglu_out[:bs], d_nk, out=self._mlp_out[:bs], pdl=self._stream_pdl)
         return self._mm(self._swiglu_out[:bs], block.mlp._d, self._mlp_out[:bs])
 
+    def head_policy(self) -> str:
+        if self._head_w is not None:
+            return (f"vocab-parallel: {self._head_w.shape[0]} of {self.vocab_size} rows per rank + b200_allgather_cols "
+                    f"({'multimem.st' if self._comm.has_multicast else 'peer stores'})")
+        return "replicated (reference: models/adapter.py:25)"
+
     def _lm_head(self, x):
         """``lm_head`` (reference :223): the weight is already in the nn.Linear layout the stream GEMM takes."""
+        if self._head_w is not None:
+            bs = x.shape[0]
+            torch.matmul(x, self._head_w.t(), out=self._logits_local[:bs])
+            return self._comm.allgather_cols(self._logits_local[:bs], self._logits[:bs])
         head = self.model.lm_head
         w = getattr(head, "weight", None)
         if (isinstance(head, torch.nn.Linear) and head.bias is None and w is not None and w.dtype == torch.bfloat16

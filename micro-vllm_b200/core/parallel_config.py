@@ -64,9 +64,10 @@ def barrier():
         dist.barrier(group=get_group() or dist.group.WORLD)
 
 
-def peer_comm(slot_bytes: int):
+def peer_comm(slot_bytes: int, gather_bytes: int = 0):
     """The node-local NVLink peer-memory communicator behind the fused all-reduce + residual +
-    RMSNorm kernel (``b200ops.comm.PeerComm``), created on first use and grown on demand; ``None``
+    RMSNorm kernel (``b200ops.comm.PeerComm``), created on first use and grown on demand (``gather_bytes``:
+    room for the logits all-gather of a vocab-parallel lm_head); ``None``
     for single-process runs, on CPU (gloo), for world sizes other than 2 / 4 / 8, or when
     ``B200_FUSED_ALLREDUCE=0`` selects the plain NCCL ``all_reduce`` + elementwise kernels
     (the reference's sequence, model_graph.py:210-219)."""
@@ -75,9 +76,11 @@ def peer_comm(slot_bytes: int):
     if os.environ.get("B200_FUSED_ALLREDUCE", "1") == "0":
         return None
     comm = _state["peer_comm"]
-    if comm is None or comm.slot_bytes < slot_bytes:
+    if comm is None or comm.slot_bytes < slot_bytes or comm.gather_bytes < gather_bytes:
         from b200ops.comm import PeerComm
         # an outgrown communicator stays mapped: captured graphs may hold its addresses
-        comm = PeerComm(slot_bytes, group=get_group() or dist.group.WORLD)
+        comm = PeerComm(max(slot_bytes, comm.slot_bytes if comm is not None else 0),
+                        group=get_group() or dist.group.WORLD,
+                        gather_bytes=max(gather_bytes, comm.gather_bytes if comm is not None else 0))
         _state["peer_comm"] = comm
     return comm

@@ -281,7 +281,8 @@ def _peer_worker(rank, world, port, q):
         pc.setup()
         dev = torch.device(f"cuda:{rank}")
         rows, n = 64, 8192
-        comm = pc.peer_comm(rows * n * 2)
+        V = 4096 * world + 64 * world                                # columns of the gathered matrix
+        comm = pc.peer_comm(rows * n * 2, gather_bytes=rows * V * 2)
         assert comm is not None and comm.world == world
         g = torch.Generator().manual_seed(100)                       # same stream of numbers on every rank
         w = (1 + 0.2 * torch.randn(n, generator=g)).to(torch.bfloat16)
@@ -457,6 +458,37 @@ def _peer_worker(rank, world, port, q):
                 assert all(torch.equal(ys[0], t) for t in ys)
                 assert _nvls_y_close(yl.cpu(), wy2, wres2, s1.abs() + s0.abs(), wres1.float(), w)
             del g5
+        # column all-gather (vocab-parallel lm_head): every rank ends up with every rank's block, eager + graph replay,
+        # with and without the multicast path; a reduction between two gathers is the WAR barrier the contract asks for
+        vs = V // world
+        src = torch.empty(rows, vs, dtype=torch.bfloat16, device=dev)
+        full = comm.gather_buf(rows, V)
+        had_mc = comm.has_multicast
+        for use_mc in ((True, False) if had_mc else (False,)):
+            comm.has_multicast = use_mc
+            comm._last_mode = None
+            for bs in (rows, 3, 1):
+                comm.allgather_cols(src[:bs], full[:bs])
+            torch.cuda.synchronize()
+            dist.barrier()
+            g6 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g6):
+                comm.allgather_cols(src, full)
+                comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yl, ro, 1e-5, True)
+                comm.allreduce_residual_rmsnorm(1, rows, n, rs, wd, yl, ro, 1e-5, True)
+            for it in range(5):
+                blocks = [torch.randn(rows, vs, generator=g).to(torch.bfloat16) for _ in range(world)]
+                src.copy_(blocks[rank].to(dev))
+                full.zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                g6.replay()
+                torch.cuda.synchronize()
+                dist.barrier()
+                assert torch.equal(full.cpu(), torch.cat(blocks, dim=1)), f"allgather_cols (multicast={use_mc}) replay {it}"
+            del g6
+        comm.has_multicast = had_mc
+        comm._last_mode = None
         assert comm.error_flag() == 0
         with pytest.raises(AssertionError):                          # same slot right after a one-shot call is refused on the host
             comm._last_slot, comm._last_mode = 1, "oneshot"

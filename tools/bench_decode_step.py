@@ -80,15 +80,17 @@ def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    # lm_head + final norm alone (replicated): needed to extrapolate 16 -> 80 layers
+    # lm_head + final norm alone, through the runner's own head path (replicated, or vocab-parallel + all-gather —
+    # every rank runs this loop, so the collective inside matches up): needed to extrapolate 16 -> 80 layers (§8d M2)
     h = torch.randn(batch, shape.hidden, device=dev, dtype=torch.bfloat16)
-    for _ in range(3):
-        model.lm_head(model.transformer.ln_f(h))
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(20):
-        model.lm_head(model.transformer.ln_f(h))
-    e1.record()
+    with torch.no_grad():
+        for _ in range(3):
+            runner._lm_head(model.transformer.ln_f(h))
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(20):
+            runner._lm_head(model.transformer.ln_f(h))
+        e1.record()
     torch.cuda.synchronize()
     head_ms = e0.elapsed_time(e1) / 20
     layers_ms = max(ms - head_ms, 0.0)
@@ -100,7 +102,8 @@ def run(shape_name="llama3-70b", layers=16, batch=64, ctx=8192, steps=20, warmup
            "setup_s": round(setup_s, 1),
            "allreduce": ("none (TP=1)" if world == 1 else
                          ("fused-" + runner._ar_mode) if runner._comm is not None else "nccl"),
-           "gemm": runner.gemm_policy(), "ar_prefetch_MB": round(runner._prefetch_bytes / 1e6, 1)}
+           "gemm": runner.gemm_policy(), "ar_prefetch_MB": round(runner._prefetch_bytes / 1e6, 1),
+           "lm_head": runner.head_policy()}
     if profile:
         # per-kernel table of the REAL TP run on rank 0 (torch.profiler / CUPTI around graph replays); under the
         # profiler kernels are serialised less tightly, so compare SHARES

@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--ctx", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--no-profile", action="store_true", help="event timing only (A/B runs of env switches)")
+    ap.add_argument("--tag", default="")
     a = ap.parse_args()
     from torch.profiler import ProfilerActivity, profile
     from core.cache_manager import KVCacheManager
@@ -69,6 +71,11 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     step_ms = e0.elapsed_time(e1) / a.steps
+    if a.no_profile:
+        print(json.dumps({"tag": a.tag, "shape": a.shape, "tp_local_of": a.tp, "layers": a.layers, "batch": a.batch,
+                          "ctx": a.ctx, "step_ms_events": round(step_ms, 4),
+                          "us_per_layer_events": round(step_ms * 1e3 / a.layers, 2), "gemm": runner.gemm_policy()}))
+        return
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         for _ in range(a.steps):
             runner.forward(tok, mgr, a.batch)
