@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 15
+#define B200_ABI_VERSION 16
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -291,6 +291,10 @@ typedef struct b200_decode_args {
  * the workspace must hold b200_decode_balanced_workspace_bytes(D) bytes (same zero-once rule);
  * B <= 512. */
 #define B200_DECODE_FLAG_BALANCED 4
+/* Split counts 2..8 launch the splits of a (sequence, kv head, group) as ONE thread-block cluster and merge the
+ * partials through distributed shared memory (no workspace needed, none touched).  This flag selects the older form:
+ * fp32 partials in the workspace, merged by the last CTA to arrive on a counter (the only form for > 8 splits). */
+#define B200_DECODE_FLAG_NO_CLUSTER 8
 
 int64_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
                                     int32_t num_splits);
@@ -396,6 +400,10 @@ void b200_debug_prefill_trace(void* dev_buf);
  * previous kernel of the stream; it waits for that kernel before reading x / residual).  Every form also releases a
  * PDL-launched SUCCESSOR at its start, so a weight-streaming GEMM behind it fetches weights during the exchange. */
 #define B200_AR_FLAG_PDL 0x100
+/* OR-ed into `mode` with B200_AR_MODE_NVLS: the owner sends y as 16-byte flag-in-data packets (multimem.st into every
+ * rank's y staging, the LL form's region: rows * n * 4 bytes) and every rank unpacks its local copy into `y` (any local
+ * tensor) — one one-way hop instead of a release fence + a counter round trip.  epoch must hold MAX_CTAS + 11 words. */
+#define B200_AR_FLAG_PACKET_TAIL 0x200
 
 typedef struct b200_ar_args {
     const void* x_peers[B200_AR_MAX_WORLD];  /* rank r's partial sums, bf16 [rows, n] (entry `rank` is local) */
@@ -421,6 +429,7 @@ typedef struct b200_ar_args {
     const void* x_mc;         /* NVLS form: multicast address of the x slot (same offset as x_peers[rank])            */
     void*       y_mc;         /* NVLS form: multicast address of the y buffer (same offset as y)                      */
     void*       flags_mc;     /* NVLS form: multicast address of the flag region (same offset as flag_peers[rank])    */
+    void*       ystage_mc;    /* NVLS form + B200_AR_FLAG_PACKET_TAIL: multicast address of the y staging             */
 } b200_ar_args;
 
 /* Row-sharded ("two-shot") form for world > 1, rows <= B200_AR_MAX_CTAS: rank r OWNS rows

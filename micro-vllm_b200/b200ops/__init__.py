@@ -264,7 +264,7 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
                       softmax_scale: Optional[float] = None, rotary_interleaved: bool = False,
                       num_splits: int = 0, out: Optional[torch.Tensor] = None,
                       softmax_lse: Optional[torch.Tensor] = None, variant: int = 0,
-                      pdl: int = 0, balanced: Optional[bool] = None) -> torch.Tensor:
+                      pdl: int = 0, balanced: Optional[bool] = None, cluster_merge: bool = True) -> torch.Tensor:
     """q [B, Hq, D]; k_new/v_new [B, Hkv, D]; caches [n_blocks, block_size, Hkv, D];
     returns out [B, Hq, D] (allocated unless given).  ``pdl`` = 1 / 2 launches with programmatic
     stream serialization, releasing the next kernel at start / after the streaming loop (see
@@ -272,7 +272,9 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     back-to-back decode kernels, so it is off by default).  ``balanced`` selects the persistent
     stream-K form (fixed grid, equal shares of all sequences' chunks per CTA, schedule derived on
     the device from ``cache_seqlens``: right for ragged and small batches); ``None`` = the
-    :func:`decode_use_balanced` heuristic; an explicit ``num_splits`` > 0 keeps the split-KV grid."""
+    :func:`decode_use_balanced` heuristic; an explicit ``num_splits`` > 0 keeps the split-KV grid.
+    ``cluster_merge``: split counts 2..8 run the splits of a segment as one thread-block cluster and merge through
+    distributed shared memory; False selects the workspace + last-arriver form (B200_DECODE_FLAG_NO_CLUSTER)."""
     _req_cuda(q, k_cache, v_cache, k_new, v_new, rotary_cos, rotary_sin, cache_seqlens, block_table)
     B, Hq, D = q.shape
     n_blocks, block_size, Hkv, Dc = k_cache.shape
@@ -324,6 +326,8 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
         variant = _tune("B200_DECODE_VARIANT")
     a.num_splits, a.variant = int(num_splits), int(variant)
     a.flags = 0 if not pdl else (_lib.DECODE_FLAG_PDL | (_lib.DECODE_FLAG_PDL_LATE if int(pdl) == 2 else 0))
+    if not cluster_merge or _tune("B200_DECODE_NO_CLUSTER") > 0:
+        a.flags |= _lib.DECODE_FLAG_NO_CLUSTER
     if balanced:
         assert not pdl, "paged_attn_decode: the balanced form has no PDL variant"
         a.flags |= _lib.DECODE_FLAG_BALANCED

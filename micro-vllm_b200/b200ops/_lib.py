@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 15
+ABI_VERSION = 16
 
 
 class DecodeArgs(C.Structure):
@@ -41,6 +41,7 @@ class DecodeArgs(C.Structure):
 DECODE_FLAG_PDL = 1
 DECODE_FLAG_PDL_LATE = 2
 DECODE_FLAG_BALANCED = 4
+DECODE_FLAG_NO_CLUSTER = 8
 DECODE_BALANCED_MAX_B = 512
 
 
@@ -73,6 +74,7 @@ AR_MODE_LL = 2
 AR_MODE_NVLS = 4
 AR_MODE_NVLS_ONEHOP = 8
 AR_FLAG_PDL = 0x100
+AR_FLAG_PACKET_TAIL = 0x200
 AR_FLAG_PDL = 0x100
 AR_NVLS_READY_WORD = AR_MAX_CTAS * (AR_MAX_WORLD + 1)
 AR_NVLS_DONE_WORD = AR_NVLS_READY_WORD + 32
@@ -89,7 +91,7 @@ class ArArgs(C.Structure):
         ("ss_rounded", _i32), ("timeout_ms", _i32), ("mode", _i32),
         ("y_peers", _vp * AR_MAX_WORLD),
         ("xstage_peers", _vp * AR_MAX_WORLD), ("ystage_peers", _vp * AR_MAX_WORLD), ("trace", _vp),
-        ("x_mc", _vp), ("y_mc", _vp), ("flags_mc", _vp),
+        ("x_mc", _vp), ("y_mc", _vp), ("flags_mc", _vp), ("ystage_mc", _vp),
     ]
 
 

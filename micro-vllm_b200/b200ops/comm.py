@@ -40,7 +40,7 @@ from ._lib import ArArgs, GatherArgs, check, lib
 # ready flags [1024][8] + done flags [1024] + the two NVLS counters (128 bytes apart)
 _FLAG_BYTES = _lib.AR_MAX_CTAS * (_lib.AR_MAX_WORLD + 1) * 4 + 256
 # per-CTA epochs, error word, LL call + arrival counters, NVLS targets + arrival counter
-_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 16) * 4 + 255) // 256 * 256
+_EPOCH_BYTES = ((_lib.AR_MAX_CTAS + 16) * 4 + 255) // 256 * 256        # words up to MAX_CTAS + 10 are in use
 _HEADER = _FLAG_BYTES + _EPOCH_BYTES
 _ERR_OFF = _FLAG_BYTES + _lib.AR_MAX_CTAS * 4
 
@@ -284,14 +284,15 @@ class PeerComm:
                                    weight: Optional[torch.Tensor], y: Optional[torch.Tensor],
                                    res_out: torch.Tensor, eps: float = 1e-6, ss_rounded: bool = False,
                                    sharded: bool = False, trace: Optional[torch.Tensor] = None, ll: bool = False,
-                                   nvls: bool = False, pdl: bool = False, nvls1: bool = False):
+                                   nvls: bool = False, pdl: bool = False, nvls1: bool = False, packet_tail: bool = False):
         """res_out = bf16(bf16(sum over ranks of slot[slot_idx][:rows, :n]) + residual);
         y = rmsnorm(res_out) * weight (skipped when weight is None).  Current stream; capturable.
         ``sharded`` / ``nvls``: the row-sharded forms (B200_AR_MODE_ROW_SHARDED, B200_AR_MODE_NVLS) —
         ``y`` must be a prefix view of :meth:`ybuf`, and ``residual`` / ``res_out`` are only read /
         written for the rows this rank owns.  ``ll``: the flag-in-data push form (same residual contract).
         ``nvls1``: the one-hop NVLS form (B200_AR_MODE_NVLS_ONEHOP: the one-shot contract — replicated residual, any
-        local ``y``, alternate slots).  ``pdl``: launch with programmatic stream serialization (B200_AR_FLAG_PDL)."""
+        local ``y``, alternate slots).  ``pdl``: launch with programmatic stream serialization (B200_AR_FLAG_PDL).  ``packet_tail`` (with ``nvls``): y
+        travels as flag-in-data packets (B200_AR_FLAG_PACKET_TAIL) and may be any local tensor."""
         assert int(sharded) + int(ll) + int(nvls) + int(nvls1) <= 1, "PeerComm: choose one of sharded / ll / nvls / nvls1"
         # "oneshot" here = no trailing barrier (peer-load one-shot and the one-hop NVLS form)
         mode = "sharded" if sharded else "ll" if ll else "nvls" if nvls else "oneshot"
@@ -319,12 +320,17 @@ class PeerComm:
                 a.y_peers[r] = self._peer_base[r] + yoff
         if nvls:
             assert self.has_multicast, "PeerComm: the NVLS form needs a multicast mapping (symm back end on an NVSwitch node)"
-            assert y is not None and y.data_ptr() == self._base + yoff and y.stride(0) == n, \
+            assert y is not None and (packet_tail or (y.data_ptr() == self._base + yoff and y.stride(0) == n)), \
                 "PeerComm: the NVLS form writes y into ybuf() on every rank"
             a.mode = _lib.AR_MODE_NVLS
             a.x_mc = self._mc_base + off
             a.y_mc = self._mc_base + yoff
             a.flags_mc = self._mc_base
+            if packet_tail:                 # y travels as flag-in-data packets through the y staging; y itself is local
+                assert rows * n * 4 <= 2 * self.slot_bytes
+                a.mode |= _lib.AR_FLAG_PACKET_TAIL
+                a.ystage_mc = self._mc_base + self._ystage_off
+                a.ystage_peers[self.rank] = self._base + self._ystage_off
         if nvls1:
             assert self.has_multicast, "PeerComm: the NVLS forms need a multicast mapping (symm back end on an NVSwitch node)"
             a.mode = _lib.AR_MODE_NVLS_ONEHOP

@@ -197,7 +197,8 @@ class ModelGraphRunner:
             self._head_w = hw.data[self.rank * vs:(self.rank + 1) * vs]          # a view: rows of the replicated matrix
             self._logits_local = torch.empty((mb, vs), dtype=dt, device=dev)
             self._logits = self._comm.gather_buf(mb, self.vocab_size)
-        # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls | nvls1; nvls1 = one-hop in-switch form).  Default: "nvls" (in-switch reduction,
+        # Reduction form (B200_AR_MODE = oneshot | sharded | ll | nvls | nvlsp | nvls1; nvls1 = one-hop in-switch form,
+        # nvlsp = two-hop in-switch form whose second hop carries flag-in-data packets instead of ending in a barrier).  Default: "nvls" (in-switch reduction,
         # multimem.ld_reduce / multimem.st on the multicast mapping of the symmetric slabs) when the communicator has
         # a multicast range and the final norm can be fused; else "ll" from 4 ranks up; else "oneshot".  "nvls", "ll"
         # and "sharded" reduce + normalise each row on ONE owner rank and keep the residual stream row-sharded, so
@@ -217,9 +218,9 @@ class ModelGraphRunner:
                     want = ("nvls" if fusable else "nvls1") if self._comm.has_multicast else "ll"
                 else:
                     want = "oneshot"
-            if want in ("nvls", "nvls1") and not self._comm.has_multicast:
+            if want in ("nvls", "nvls1", "nvlsp") and not self._comm.has_multicast:
                 want = "ll" if self.world_size >= 4 else "oneshot"
-            if want in ("ll", "sharded", "nvls") and fusable:
+            if want in ("ll", "sharded", "nvls", "nvlsp") and fusable:
                 self._ar_mode = want
             if want == "nvls1":                         # one-hop in-switch form: the one-shot contract, no ln_f condition
                 self._ar_mode = want
@@ -352,8 +353,9 @@ class ModelGraphRunner:
             self._comm.allreduce_residual_rmsnorm(slot, x.shape[0], self.hidden_dim, residual, w,
                                                   y if norm is not None else None, res_out, eps, ss_rounded,
                                                   sharded=self._ar_mode == "sharded", ll=self._ar_mode == "ll",
-                                                  nvls=self._ar_mode == "nvls", pdl=self._ar_pdl,
-                                                  nvls1=self._ar_mode == "nvls1")
+                                                  nvls=self._ar_mode in ("nvls", "nvlsp"), pdl=self._ar_pdl,
+                                                  nvls1=self._ar_mode == "nvls1",
+                                                  packet_tail=self._ar_mode == "nvlsp")
         else:
             all_reduce(x)                                   # NCCL when TP without peer memory; no-op at TP=1
             allreduce_residual_rmsnorm_local(x, residual, w, y if norm is not None else None, res_out, eps,

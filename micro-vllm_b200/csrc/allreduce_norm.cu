@@ -45,6 +45,7 @@ struct ArParams {
     __nv_bfloat16* y_mc;                    // NVLS form: multicast address of the y buffer (multimem.st)
     uint32_t* flags_mc;                     // NVLS form: multicast address of the flag region (multimem.red)
     int pdl;                                // launched with programmatic stream serialization: wait for the previous kernel
+    uint8_t* ystage_mc;                     // NVLS form with the packet tail: multicast address of the y staging
 };
 
 __device__ __forceinline__ void stamp(const ArParams& p, int slot) {
@@ -455,6 +456,7 @@ allreduce_ll_kernel(const __grid_constant__ ArParams p) {
 #define B200_AR_EPOCH_NVLS_READY (B200_AR_MAX_CTAS + 4)                                // local targets / arrival counter
 #define B200_AR_EPOCH_NVLS_DONE  (B200_AR_MAX_CTAS + 5)
 #define B200_AR_EPOCH_NVLS_ARRIVE (B200_AR_MAX_CTAS + 6)
+#define B200_AR_EPOCH_NVLS_CALL (B200_AR_MAX_CTAS + 10)                                // packet-tail form: call counter = packet flag
 
 __device__ __forceinline__ void multimem_red_add_relaxed(uint32_t* mc, uint32_t v) {
     asm volatile("multimem.red.relaxed.sys.global.add.u32 [%0], %1;" :: "l"(mc), "r"(v) : "memory");
@@ -482,7 +484,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // per requester — 1 MB per GPU at decode sizes, far below NVLink bandwidth), adds its REPLICATED residual, normalises
 // and stores y locally.  No second hop and no trailing barrier: like the one-shot peer-load form, consecutive calls
 // must alternate x slots, and res_out / residual are full tensors on every rank.
-template <int VPT, typename WT, bool ONE>
+// PKT = the two-hop form with a PACKET tail: the owner multimem.st's y as 16-byte packets {d0, e, d1, e} (e = call
+// counter) into every rank's y staging, and every rank's CTAs poll their LOCAL staging and unpack it into the plain y.
+// That replaces "multimem.red.release per CTA (a system-scope fence behind 16 KB of multicast stores) + wait for all
+// 8 x grid arrivals" — 6.7 us of the 16.4 us kernel at 8 ranks (profiles/r02/allreduce_tp8.json) — by one one-way hop.
+template <int VPT, typename WT, bool ONE, bool PKT>
 __global__ void __launch_bounds__(1024)
 allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
     __shared__ float red[32];
@@ -495,6 +501,10 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
     stamp(p, 0);
     const uint32_t ready_t = p.epoch[B200_AR_EPOCH_NVLS_READY] + (uint32_t)world;
     const uint32_t done_t = p.epoch[B200_AR_EPOCH_NVLS_DONE] + (uint32_t)world * gridDim.x;
+    // packet flag of this call; the top bit keeps it apart from the LL form's call numbers (same staging region)
+    const uint32_t pkt_n = p.epoch[B200_AR_EPOCH_NVLS_CALL] + 1u;
+    const uint32_t pkt_e = 0x80000000u | pkt_n;
+    const size_t row_stage = (size_t)nvec * 32;             // bytes of one staged row (2 packets per 16-byte vector)
     uint32_t* my_flags = p.flags[p.rank];
     if (threadIdx.x == 0) {
         // x was written by the kernel that precedes this one in the stream: no fence needed (see st_relaxed_sys)
@@ -565,15 +575,45 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     po[k] = pack_bf16(f[i][2 * k] * rrms * wf[2 * k], f[i][2 * k + 1] * rrms * wf[2 * k + 1]);
-                if constexpr (ONE) st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
-                else multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);  // lands in every rank's y buffer
+                if constexpr (ONE) {
+                    st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
+                } else if constexpr (PKT) {
+                    uint8_t* dst = p.ystage_mc + (size_t)row * row_stage + (size_t)v * 32;
+                    multimem_st_v4(dst, make_uint4(o.x, pkt_e, o.y, pkt_e));
+                    multimem_st_v4(dst + 16, make_uint4(o.z, pkt_e, o.w, pkt_e));
+                } else {
+                    multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);  // lands in every rank's y buffer
+                }
             }
         }
     }
     stamp(p, 2);
+    if constexpr (PKT) {
+        // every rank unpacks ALL rows from its local staging (this rank's CTAs share them); a packet is complete when
+        // both flag words carry this call's number
+        const uint8_t* mine = p.ystage[p.rank];
+        for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+#pragma unroll
+            for (int i = 0; i < VPT; ++i) {
+                const int v = threadIdx.x + i * T;
+                if (v < nvec) {
+                    const uint8_t* src = mine + (size_t)row * row_stage + (size_t)v * 32;
+                    uint4 a = ld_peer_v4(src), b = ld_peer_v4(src + 16);
+                    if (!ll_ready(a, pkt_e) || !ll_ready(b, pkt_e)) {
+                        const long long t0 = now_ns();
+                        do {
+                            a = ld_peer_v4(src); b = ld_peer_v4(src + 16);
+                            if (now_ns() - t0 > p.timeout_ns) { atomicExch(p.epoch + B200_AR_MAX_CTAS, 1u); break; }
+                        } while (!ll_ready(a, pkt_e) || !ll_ready(b, pkt_e));
+                    }
+                    st_na_v4(p.y + row * p.sy + (int64_t)v * 8, make_uint4(a.x, a.z, b.x, b.z));
+                }
+            }
+        }
+    }
     __syncthreads();                                         // every thread's multimem.st is ordered before the release below
     if (threadIdx.x == 0) {
-        if constexpr (!ONE) {
+        if constexpr (!ONE && !PKT) {
             multimem_red_add_release(p.flags_mc + B200_AR_NVLS_DONE_WORD, 1u);
             // all CTAs of all ranks have stored their rows (and finished reading x)
             if ((int32_t)(ld_acquire_sys(my_flags + B200_AR_NVLS_DONE_WORD) - done_t) < 0) {
@@ -588,23 +628,24 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
         if (arrived == gridDim.x - 1) {
             p.epoch[B200_AR_EPOCH_NVLS_ARRIVE] = 0u;
             p.epoch[B200_AR_EPOCH_NVLS_READY] = ready_t;
-            if constexpr (!ONE) p.epoch[B200_AR_EPOCH_NVLS_DONE] = done_t;
+            if constexpr (!ONE && !PKT) p.epoch[B200_AR_EPOCH_NVLS_DONE] = done_t;
+            if constexpr (PKT) p.epoch[B200_AR_EPOCH_NVLS_CALL] = pkt_n & 0x7fffffffu;
         }
     }
     stamp(p, 3);
 }
 
-template <typename WT, bool ONE>
+template <typename WT, bool ONE, bool PKT>
 static int launch_nvls(const ArParams& p, int world, cudaStream_t st) {
     const int64_t nvec = p.n / 8;
     const int64_t my_rows = ONE ? p.rows : (int64_t)p.rows_per_rank;
     const unsigned grid = (unsigned)(my_rows < 128 ? my_rows : 128);   // all resident at once (148 SMs)
     if (nvec <= 1024) {
         int threads = (int)((nvec + 31) & ~31LL);
-        B200_LAUNCH_AR((allreduce_nvls_kernel<1, WT, ONE>), grid, threads, st, p.pdl != 0, p, world);
+        B200_LAUNCH_AR((allreduce_nvls_kernel<1, WT, ONE, PKT>), grid, threads, st, p.pdl != 0, p, world);
     } else {
         int threads = (int)((((nvec + 1) / 2) + 31) & ~31LL);
-        B200_LAUNCH_AR((allreduce_nvls_kernel<2, WT, ONE>), grid, threads, st, p.pdl != 0, p, world);
+        B200_LAUNCH_AR((allreduce_nvls_kernel<2, WT, ONE, PKT>), grid, threads, st, p.pdl != 0, p, world);
     }
     B200_CHECK_LAUNCH();
     return 0;
@@ -814,7 +855,8 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         if (a->world < 2) B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: NVLS form needs world > 1");
         if (!a->weight) B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the norm (weight, y)");
         if (nvls1 && (a->mode & B200_AR_MODE_NVLS)) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: choose one of NVLS / NVLS_ONEHOP");
-        if (!a->x_mc || !a->flags_mc || !aligned16(a->x_mc) || (!nvls1 && (!a->y_mc || !aligned16(a->y_mc))))
+        if (!a->x_mc || !a->flags_mc || !aligned16(a->x_mc) ||
+            (!nvls1 && !(a->mode & B200_AR_FLAG_PACKET_TAIL) && (!a->y_mc || !aligned16(a->y_mc))))
             B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: NVLS form needs the multicast addresses of x, y and the flags");
         if (a->rows > 65535LL * a->world) B200_FAIL(B200_E_RANGE, "allreduce_residual_rmsnorm: NVLS form: too many rows");
         p.x_mc = (const __nv_bfloat16*)a->x_mc;
@@ -838,13 +880,22 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
     p.pdl = (a->mode & B200_AR_FLAG_PDL) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
     if (nvls1) {
-        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, true>(p, a->world, st);
-        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, true>(p, a->world, st);
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, true, false>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, true, false>(p, a->world, st);
+        B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
+    }
+    if (nvls && (a->mode & B200_AR_FLAG_PACKET_TAIL)) {
+        if (!a->ystage_mc || !aligned16(a->ystage_mc) || !a->ystage_peers[a->rank] || !aligned16(a->ystage_peers[a->rank]))
+            B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: the packet tail needs ystage_mc and ystage_peers[rank]");
+        p.ystage_mc = (uint8_t*)a->ystage_mc;
+        p.ystage[a->rank] = (uint8_t*)a->ystage_peers[a->rank];
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, false, true>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, false, true>(p, a->world, st);
         B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
     }
     if (nvls) {
-        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, false>(p, a->world, st);
-        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, false>(p, a->world, st);
+        if (a->w_dtype == B200_DT_F32) return launch_nvls<float, false, false>(p, a->world, st);
+        if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, false, false>(p, a->world, st);
         B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
     }
     if (ll) {

@@ -60,6 +60,7 @@ struct DecodeParams {
     int page_shift;                      // log2(block_size) or -1 when block_size is not a power of two
     int pdl;                             // launched with programmatic stream serialization
     unsigned long long* trace;           // debug only (b200_debug_decode_trace): [CTA][8] %globaltimer stamps
+    int cluster;                         // the splits of a segment form one thread-block cluster: merge through DSMEM
     int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, o_sb, o_sh;
     int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
     float scale, scale_log2;
@@ -89,7 +90,11 @@ struct DCfg {
     static constexpr int KV_B = NWARPS * STAGES * STAGE_B;
     static constexpr int OPAD = D + 8;               // fp32 row pitch of the warp-merge buffer
     static constexpr int RED_B = NWARPS * 16 * OPAD * 4 + NWARPS * 16 * 2 * 4;
-    static constexpr int MAIN_B = KV_B > RED_B ? KV_B : RED_B;
+    // split merge through distributed shared memory: [16][D] fp32 normalised partial + [16] lse per CTA, placed BEHIND
+    // the warp-merge scratch (it is written by the sink that reads that scratch)
+    static constexpr int CL_OFF = (RED_B + 127) / 128 * 128;
+    static constexpr int CL_B = 16 * D * 4 + 64;
+    static constexpr int MAIN_B = (KV_B > CL_OFF + CL_B) ? KV_B : (CL_OFF + CL_B);
     static constexpr int Q_B = 16 * ROWB;
     static constexpr int NEW_B = 2 * ROWB;
     static constexpr int SMEM = MAIN_B + Q_B + NEW_B + 64;
@@ -408,6 +413,18 @@ __device__ __forceinline__ void decode_piece(const DecodeParams& p, uint8_t* sme
     }
 }
 
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t cta_rank) {
+    uint32_t remote;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(cta_rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+    return v;
+}
+
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
 paged_decode_kernel(const __grid_constant__ DecodeParams p) {
@@ -432,10 +449,16 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     pc.c1 = min(pc.n_chunks, pc.c0 + cps);
     const int64_t bh0 = (int64_t)b * p.Hq + hq0;
 
+    float* c_o = reinterpret_cast<float*>(smem + C::CL_OFF);     // [16][D] this CTA's normalised partial (cluster form)
+    float* c_lse = c_o + 16 * D;                                 // [16]
+    const bool clustered = p.cluster != 0;
     decode_piece<C>(p, smem, pc, true, [&](int g, int d, float val, float lse) {
         if (S == 1) {
             p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(val);
             if (d == 0 && p.lse_out) p.lse_out[bh0 + g] = lse;
+        } else if (clustered) {
+            c_o[g * D + d] = val;
+            if (d == 0) c_lse[g] = lse;
         } else {
             p.ws_o[((bh0 + g) * S + split) * D + d] = val;
             if (d == 0) p.ws_lse[(bh0 + g) * S + split] = lse;
@@ -443,6 +466,47 @@ paged_decode_kernel(const __grid_constant__ DecodeParams p) {
     });
     dec_stamp(p, 5);
     if (S == 1) return;
+
+    if (clustered) {
+        // ---- the S CTAs of this (b, kv head, group) are ONE thread-block cluster (cluster rank = split): every CTA
+        // merges an equal slice of the outputs, reading all S partials through distributed shared memory — no global
+        // scratch, no atomics, no L2 round trips (the global form's last-arriver merge took 6.4 us at S = 4,
+        // profiles/r02/trace_decode.log).  Same arithmetic and summation order as the global form.
+        cluster_sync_all();
+        const int total = gcount * D;
+        const int per = (total + S - 1) / S;
+        const int lo = split * per, hi = min(total, lo + per);
+        const uint32_t o_addr = smem_u32(c_o), l_addr = smem_u32(c_lse);
+        for (int idx = lo + tid; idx < hi; idx += C::THREADS) {
+            const int g = idx / D, d = idx - g * D;
+            float w[8];
+            float mx = -CUDART_INF_F;
+#pragma unroll
+            for (int s2 = 0; s2 < 8; ++s2) {
+                w[s2] = (s2 < S) ? ld_dsmem_f32(l_addr + g * 4, (uint32_t)s2) : -CUDART_INF_F;
+                mx = fmaxf(mx, w[s2]);
+            }
+            const float mref = (mx == -CUDART_INF_F) ? 0.0f : mx;
+            float sum = 0.0f;
+#pragma unroll
+            for (int s2 = 0; s2 < 8; ++s2) {
+                w[s2] = (s2 < S) ? __expf(w[s2] - mref) : 0.0f;
+                sum += w[s2];
+            }
+            const float inv = (sum > 0.0f) ? 1.0f / sum : 0.0f;
+            float acc = 0.0f;
+#pragma unroll
+            for (int s2 = 0; s2 < 8; ++s2) {
+                const float ws2 = w[s2] * inv;
+                if (s2 < S && ws2 != 0.0f) acc += ws2 * ld_dsmem_f32(o_addr + idx * 4, (uint32_t)s2);
+            }
+            p.out[(int64_t)b * p.o_sb + (int64_t)(hq0 + g) * p.o_sh + d] = __float2bfloat16_rn(acc);
+            if (d == 0 && p.lse_out) p.lse_out[bh0 + g] = (sum > 0.0f) ? (mref + __logf(sum)) : -CUDART_INF_F;
+        }
+        cluster_sync_all();                              // nobody exits while its shared memory is still being read
+        dec_stamp(p, 7);
+        return;
+    }
 
     // ---- split merge by the last-arriving CTA of this (b, kv head, group)
     __syncthreads();
@@ -729,13 +793,22 @@ static int launch_decode(const DecodeParams& p, int S, cudaStream_t st) {
         attr_done = true; attr_dev = dev;
     }
     dim3 grid((unsigned)S, (unsigned)(p.Hkv * p.ngroups), (unsigned)p.B);
-    if (p.pdl) {
+    if (p.pdl || p.cluster) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = grid; cfg.blockDim = dim3(C::THREADS); cfg.dynamicSmemBytes = C::SMEM; cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (p.pdl) {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
+        if (p.cluster) {                                 // the S splits of a segment = one cluster along x
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = (unsigned)S; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        cfg.attrs = attr; cfg.numAttrs = na;
         cudaError_t e = cudaLaunchKernelEx(&cfg, paged_decode_kernel<C>, p);
         if (e != cudaSuccess) { set_error("decode: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     } else {
@@ -806,6 +879,8 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
         p.counters = (int32_t*)(ws + w.counters_off);
         p.ws_lse = (float*)(ws + w.lse_off);
         p.ws_o = (float*)(ws + w.o_off);
+    } else if (S > 1 && S <= 8 && !(a->flags & B200_DECODE_FLAG_NO_CLUSTER)) {
+        p.counters = nullptr; p.ws_lse = nullptr; p.ws_o = nullptr;      // merged through distributed shared memory
     } else if (S > 1) {
         if ((int64_t)a->B * a->Hkv * ngroups > kMaxCounters)
             B200_FAIL(B200_E_RANGE, "decode: B * Hkv * groups = %lld exceeds the %lld split-merge counters",
@@ -831,6 +906,7 @@ extern "C" int b200_paged_attn_decode(const b200_decode_args* a, void* stream) {
     p.page_shift = -1;
     for (int sft = 5; sft < 31; ++sft) if ((1 << sft) == a->block_size) p.page_shift = sft;
     p.trace = balanced ? nullptr : g_dec_trace;
+    p.cluster = (!balanced && S > 1 && S <= 8 && !(a->flags & B200_DECODE_FLAG_NO_CLUSTER)) ? 1 : 0;
     p.pdl = (a->flags & B200_DECODE_FLAG_PDL) ? ((a->flags & B200_DECODE_FLAG_PDL_LATE) ? 2 : 1) : 0;
     p.q_sb = a->q_stride_b; p.q_sh = a->q_stride_h; p.k_sb = a->k_stride_b; p.k_sh = a->k_stride_h;
     p.v_sb = a->v_stride_b; p.v_sh = a->v_stride_h; p.o_sb = a->o_stride_b; p.o_sh = a->o_stride_h;

@@ -380,44 +380,46 @@ def _peer_worker(rank, world, port, q):
         # the sharded form; the in-switch fp32 sum is rounded once, so the residual stream may differ from the
         # rank-order oracle by the last bf16 ulp; every rank gets the SAME y (one computation, multicast store)
         if comm.has_multicast:
-            g4 = torch.cuda.CUDAGraph()
-            for bs in (rows, 7, 1, rows):                        # row partitions (and grids) change between calls
-                comm.allreduce_residual_rmsnorm(0, bs, n, rs[:bs], wd, yb[:bs], ro[:bs], 1e-5, True, nvls=True)
-            torch.cuda.synchronize()
-            dist.barrier()
-            with torch.cuda.graph(g4):
-                comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yb, ro, 1e-5, True, nvls=True)
-                comm.allreduce_residual_rmsnorm(0, rows, n, ro, wd, yb, rs, 1e-5, False, nvls=True)
-            for it in range(10):
-                parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
-                r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
-                xs[0].copy_(parts0[rank].to(dev))
-                rs.copy_(r.to(dev))
+            for pkt in (False, True):                                # second hop: multicast stores + barrier / flag-in-data packets
+                yb_ = yl if pkt else yb
+                g4 = torch.cuda.CUDAGraph()
+                for bs in (rows, 7, 1, rows):                        # row partitions (and grids) change between calls
+                    comm.allreduce_residual_rmsnorm(0, bs, n, rs[:bs], wd, yb_[:bs], ro[:bs], 1e-5, True, nvls=True, packet_tail=pkt)
                 torch.cuda.synchronize()
                 dist.barrier()
-                g4.replay()
-                torch.cuda.synchronize()
-                dist.barrier()
-                wy1, wres1 = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, True)
-                wy2, wres2 = allreduce_residual_rmsnorm_oracle(parts0, wres1, w, 1e-5, False)
-                # the in-switch sum may round differently from the rank-order fp32 sum by one bf16 ulp OF THE SUM (which,
-                # after the residual add, can be many ulps of a small result): tolerance in units of the operands
-                ssum = sum(p_.float() for p_ in parts0)
-                for got_, want_, res_in in ((ro, wres1, r.float()), (rs, wres2, wres1.float())):
-                    err = (got_[lo:hi].float().cpu() - want_[lo:hi].float()).abs()
-                    tol = 2.0 ** -7 * ssum[lo:hi].abs() + 2.0 ** -7 * want_[lo:hi].float().abs() + 2.0 ** -7 * res_in[lo:hi].abs()
-                    assert bool((err <= tol).all()), f"nvls replay {it}: residual stream off by {float((err / tol.clamp_min(1e-9)).max()):.2f} x tol"
-                # rounding points of this form are the REFERENCE's (all_reduce rounds the sum to bf16, the residual add
-                # rounds again, model_graph.py:170-172) and so are the oracle's; the switch's own f32 -> bf16 conversion of
-                # the sum is not documented (tools/bench_allreduce.py measures which rounding it is), so most, not all,
-                # elements are bit-identical and the rest sit inside the operand-unit bound above
-                frac_same = float((ro[lo:hi].cpu() == wres1[lo:hi]).float().mean())
-                assert frac_same > 0.75, f"nvls: only {frac_same:.3f} of the reduced rows bit-identical to the oracle"
-                ys = [torch.empty_like(yb) for _ in range(world)]
-                dist.all_gather(ys, yb.contiguous())
-                assert all(torch.equal(ys[0], t) for t in ys), "every rank must hold the same normalised rows"
-                assert _nvls_y_close(yb.cpu(), wy2, wres2, ssum, wres1.float(), w)
-            del g4
+                with torch.cuda.graph(g4):
+                    comm.allreduce_residual_rmsnorm(0, rows, n, rs, wd, yb_, ro, 1e-5, True, nvls=True, packet_tail=pkt)
+                    comm.allreduce_residual_rmsnorm(0, rows, n, ro, wd, yb_, rs, 1e-5, False, nvls=True, packet_tail=pkt)
+                for it in range(10):
+                    parts0 = [(torch.randn(rows, n, generator=g)).to(torch.bfloat16) for _ in range(world)]
+                    r = torch.randn(rows, n, generator=g).to(torch.bfloat16)
+                    xs[0].copy_(parts0[rank].to(dev))
+                    rs.copy_(r.to(dev))
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    g4.replay()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    wy1, wres1 = allreduce_residual_rmsnorm_oracle(parts0, r, w, 1e-5, True)
+                    wy2, wres2 = allreduce_residual_rmsnorm_oracle(parts0, wres1, w, 1e-5, False)
+                    # the in-switch sum may round differently from the rank-order fp32 sum by one bf16 ulp OF THE SUM (which,
+                    # after the residual add, can be many ulps of a small result): tolerance in units of the operands
+                    ssum = sum(p_.float() for p_ in parts0)
+                    for got_, want_, res_in in ((ro, wres1, r.float()), (rs, wres2, wres1.float())):
+                        err = (got_[lo:hi].float().cpu() - want_[lo:hi].float()).abs()
+                        tol = 2.0 ** -7 * ssum[lo:hi].abs() + 2.0 ** -7 * want_[lo:hi].float().abs() + 2.0 ** -7 * res_in[lo:hi].abs()
+                        assert bool((err <= tol).all()), f"nvls replay {it}: residual stream off by {float((err / tol.clamp_min(1e-9)).max()):.2f} x tol"
+                    # rounding points of this form are the REFERENCE's (all_reduce rounds the sum to bf16, the residual add
+                    # rounds again, model_graph.py:170-172) and so are the oracle's; the switch's own f32 -> bf16 conversion of
+                    # the sum is not documented (tools/bench_allreduce.py measures which rounding it is), so most, not all,
+                    # elements are bit-identical and the rest sit inside the operand-unit bound above
+                    frac_same = float((ro[lo:hi].cpu() == wres1[lo:hi]).float().mean())
+                    assert frac_same > 0.75, f"nvls: only {frac_same:.3f} of the reduced rows bit-identical to the oracle"
+                    ys = [torch.empty_like(yb_) for _ in range(world)]
+                    dist.all_gather(ys, yb_.contiguous())
+                    assert all(torch.equal(ys[0], t) for t in ys), "every rank must hold the same normalised rows"
+                    assert _nvls_y_close(yb_.cpu(), wy2, wres2, ssum, wres1.float(), w)
+                del g4
             # one-hop in-switch form: the one-shot contract (replicated residual, local y, alternating slots)
             yl = torch.empty(rows, n, dtype=torch.bfloat16, device=dev)
             ra, rb = torch.empty_like(yl), torch.empty_like(yl)

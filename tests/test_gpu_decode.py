@@ -16,7 +16,8 @@ from _cases import assert_close, make_paged_case, to_dev
 pytestmark = pytest.mark.gpu
 
 
-def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rotary=True, balanced=None):
+def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rotary=True, balanced=None,
+             cluster_merge=True):
     d = to_dev(case)
     kc_ref, vc_ref = case["k_cache"].clone(), case["v_cache"].clone()
     want = paged_attention_oracle(case["q"], kc_ref, vc_ref,
@@ -28,7 +29,7 @@ def run_both(case, interleaved=False, num_splits=0, variant=0, append=True, rota
         d["k"][:, 0] if append else None, d["v"][:, 0] if append else None,
         d["cos"] if rotary else None, d["sin"] if rotary else None,
         d["seqlens"], d["table"], softmax_scale=case["scale"], rotary_interleaved=interleaved,
-        num_splits=num_splits, variant=variant, balanced=balanced)
+        num_splits=num_splits, variant=variant, balanced=balanced, cluster_merge=cluster_merge)
     torch.cuda.synchronize()
     return got, want[:, 0], d, kc_ref, vc_ref
 
@@ -62,6 +63,30 @@ def test_split_counts(num_splits):
     lens = [4095, 3000, 257, 5, 0, 2047, 2048, 1023]
     case = make_paged_case(8, 32, 8, 128, lens, seed=num_splits)
     check(case, num_splits=num_splits)
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (28, 4, 128), (14, 2, 64), (8, 1, 128)])
+@pytest.mark.parametrize("num_splits", [2, 4, 5, 8])
+def test_cluster_merge_equals_workspace_merge(num_splits, Hq, Hkv, D):
+    """Split counts 2..8 merge the splits of a segment through distributed shared memory (one thread-block cluster per
+    segment); the workspace + last-arriver form does the same arithmetic in the same order: bit-identical outputs and
+    lse, with empty splits (short rows) and every variant's shared-memory layout."""
+    lens = [4095, 3000, 257, 5, 0, 2047, 2048, 1023, 64, 1]
+    case = make_paged_case(len(lens), Hq, Hkv, D, lens, seed=num_splits * 7 + Hq)
+    a = check(case, num_splits=num_splits, cluster_merge=True)
+    b = check(case, num_splits=num_splits, cluster_merge=False)
+    assert torch.equal(a, b)
+    for v in ([1, 5, 8] if D == 128 else [2]):
+        a = check(case, num_splits=num_splits, variant=v, cluster_merge=True)
+        b = check(case, num_splits=num_splits, variant=v, cluster_merge=False)
+        assert torch.equal(a, b), f"variant {v}"
+    d = to_dev(case)
+    lse = [torch.empty(len(lens) * Hq, dtype=torch.float32, device="cuda") for _ in range(2)]
+    for i, cm in enumerate((True, False)):
+        b200ops.paged_attn_decode(d["q"][:, 0], d["k_cache"].clone(), d["v_cache"].clone(), d["k"][:, 0], d["v"][:, 0],
+                                  d["cos"], d["sin"], d["seqlens"], d["table"], softmax_scale=case["scale"],
+                                  softmax_lse=lse[i], num_splits=num_splits, cluster_merge=cm)
+    assert torch.equal(lse[0], lse[1])
 
 
 @pytest.mark.parametrize("D,variants", [(128, [1, 2, 3, 4, 5, 6, 7, 8]), (64, [1, 2, 3])])

@@ -5,6 +5,7 @@
   sharded  : row-sharded form (owner reduces its rows, pushes y to all ranks)
   ll       : LL push form (flag-in-data packets, remote stores only)
   nvls     : in-switch reduction (multimem.ld_reduce / multimem.st on the multicast mapping; needs the symm back end)
+  nvlsp    : nvls with a packet tail (y as flag-in-data packets; no release fence, no done counter)
   nvls1    : one-hop in-switch form (every rank pulls the sum of every row; no second hop, no trailing barrier)
   nccl     : dist.all_reduce + the local fused residual+norm kernel (B200_FUSED_ALLREDUCE=0 path)
 
@@ -56,7 +57,8 @@ def main():
                                                 yb if mode in ("sharded", "nvls") else y_loc,
                                                 res_b if c & 1 == 0 else res_a, 1e-5,
                                                 bool(c & 1), sharded=mode == "sharded", ll=mode == "ll",
-                                                nvls=mode == "nvls", nvls1=mode == "nvls1",
+                                                nvls=mode in ("nvls", "nvlsp"), nvls1=mode == "nvls1",
+                                                packet_tail=mode == "nvlsp",
                                                 trace=tr if c == calls - 1 else None)
 
         def nccl():
@@ -92,7 +94,7 @@ def main():
 
         row = {"world": world, "rows": rows, "n": n, "bytes_per_rank": rows * n * 2, "backend": comm.backend,
                "multicast": comm.has_multicast}
-        modes = ("oneshot", "sharded", "ll") + (("nvls", "nvls1") if comm.has_multicast else ())
+        modes = ("oneshot", "sharded", "ll") + (("nvls", "nvlsp", "nvls1") if comm.has_multicast else ())
         # correctness of every form against an fp32 NCCL sum of the same slot (one call, slot 0, no residual stream reuse)
         R = -(-rows // world)
         own = slice(rank * R, min(rows, (rank + 1) * R))
@@ -110,10 +112,11 @@ def main():
             dist.barrier()
             comm._last_mode = None        # every rank is past the barrier above: nobody still reads either slot
             comm.allreduce_residual_rmsnorm(1, rows, n, resid, w, yo, torch.empty_like(ro), 1e-5, True,
-                                            sharded=name == "sharded", ll=name == "ll", nvls=name == "nvls",
-                                            nvls1=name == "nvls1")  # slot alternation
+                                            sharded=name == "sharded", ll=name == "ll", nvls=name in ("nvls", "nvlsp"),
+                                            nvls1=name == "nvls1", packet_tail=name == "nvlsp")  # slot alternation
             comm.allreduce_residual_rmsnorm(0, rows, n, resid, w, yo, ro, 1e-5, True, sharded=name == "sharded",
-                                            ll=name == "ll", nvls=name == "nvls", nvls1=name == "nvls1")
+                                            ll=name == "ll", nvls=name in ("nvls", "nvlsp"), nvls1=name == "nvls1",
+                                            packet_tail=name == "nvlsp")
             torch.cuda.synchronize()
             dist.barrier()
             sl = slice(0, rows) if name in ("oneshot", "nvls1") else own
