@@ -395,29 +395,32 @@ def run_b200_arm(args):
 
     qkv_host = torch.randn(L, B, (Hq_l + 2 * Hkv_l) * D, dtype=torch.float32).to(torch.bfloat16).pin_memory()
     out_host = torch.empty(L, B, Hq_l * D, dtype=torch.bfloat16).pin_memory()
-    qkv_dev = torch.empty_like(qkv_host, device=dev)
-    out_dev = torch.empty(L, B, Hq_l, D, dtype=torch.bfloat16, device=dev)
-    qkv_dev.copy_(qkv_host)
+    # two device-side sets of step inputs / outputs: the e2e leg copies step t+1 in and step t-1 out while step t runs
+    qkv_devs = [torch.empty_like(qkv_host, device=dev) for _ in range(2)]
+    out_devs = [torch.empty(L, B, Hq_l, D, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    qkv_dev, out_dev = qkv_devs[0], out_devs[0]
+    for t_ in qkv_devs:
+        t_.copy_(qkv_host)
     block_table, seqlens = mgr.cache_batch_data(seq_ids, lens)
     num_splits = args.splits if args.splits > 0 else 0
 
-    def layer_call(l):
-        x = qkv_dev[l]
+    def layer_call(l, s_=0):
+        x = qkv_devs[s_][l]
         q = x[:, : Hq_l * D].view(B, Hq_l, D)
         k = x[:, Hq_l * D: (Hq_l + Hkv_l) * D].view(B, Hkv_l, D)
         v = x[:, (Hq_l + Hkv_l) * D:].view(B, Hkv_l, D)
         b200ops.paged_attn_decode(q, mgr.k_caches[l], mgr.v_caches[l], k, v, cos, sin, seqlens, block_table,
-                                  rotary_interleaved=False, out=out_dev[l], num_splits=num_splits,
+                                  rotary_interleaved=False, out=out_devs[s_][l], num_splits=num_splits,
                                   variant=args.variant, pdl=args.pdl)
 
-    def layers(lo, hi):
+    def layers(lo, hi, s_=0):
         for l in range(lo, hi):
-            layer_call(l)
+            layer_call(l, s_)
 
     graph = _graph_of(lambda: layers(0, L))      # the 32 launches of one decode step in one graph
     n_chunks = 8                                 # e2e: host<->device copies pipelined against compute
     bounds = [(c * L // n_chunks, (c + 1) * L // n_chunks) for c in range(n_chunks)]
-    chunk_graphs = [_graph_of(lambda lo=lo, hi=hi: layers(lo, hi)) for lo, hi in bounds]
+    chunk_graphs = [[_graph_of(lambda lo=lo, hi=hi, s_=s_: layers(lo, hi, s_)) for lo, hi in bounds] for s_ in (0, 1)]
 
     def sync_all():
         if world > 1:
@@ -450,42 +453,48 @@ def run_b200_arm(args):
     achieved = bytes_layer_local / (kernel_us * 1e-6) / 1e9
 
     # ---- e2e: host buffers in, host buffers out, metadata rebuilt from Python lists every step.
-    # The layers are driven in 8 chunks so that the H2D copy of chunk c+1 and the D2H copy of
-    # chunk c-1 overlap the attention of chunk c (two copy streams + events); every byte still
-    # crosses PCIe inside the timed region.
+    # The layers are driven in 8 chunks so that the H2D copy of chunk c+1 and the D2H copy of chunk c-1 overlap the
+    # attention of chunk c (two copy streams + events), and the device-side input / output sets alternate between
+    # steps so that the copies of neighbouring steps overlap too; every byte still crosses PCIe inside the timed region.
     main = torch.cuda.current_stream()
     h2d_s, d2h_s = torch.cuda.Stream(), torch.cuda.Stream()
-    ev_in = [torch.cuda.Event() for _ in range(n_chunks)]
-    ev_out = [torch.cuda.Event() for _ in range(n_chunks)]
-    ev_step = torch.cuda.Event()
-    out_view = out_dev.view(L, B, Hq_l * D)
+    ev_in = [[torch.cuda.Event() for _ in range(n_chunks)] for _ in (0, 1)]
+    ev_out = [[torch.cuda.Event() for _ in range(n_chunks)] for _ in (0, 1)]
+    ev_consumed = [torch.cuda.Event() for _ in (0, 1)]      # the step that used input set s has read all of it
+    ev_drained = [torch.cuda.Event() for _ in (0, 1)]       # output set s has been copied back to the host
+    out_views = [o.view(L, B, Hq_l * D) for o in out_devs]
+    step_no = [0]
 
     def e2e_step():
+        s_ = step_no[0] & 1
+        step_no[0] += 1
         mgr.cache_batch_data(seq_ids, lens)
-        h2d_s.wait_event(ev_step)                       # previous step's compute has consumed qkv_dev
+        h2d_s.wait_event(ev_consumed[s_])
         with torch.cuda.stream(h2d_s):
             for c, (lo, hi) in enumerate(bounds):
-                qkv_dev[lo:hi].copy_(qkv_host[lo:hi], non_blocking=True)
-                ev_in[c].record(h2d_s)
+                qkv_devs[s_][lo:hi].copy_(qkv_host[lo:hi], non_blocking=True)
+                ev_in[s_][c].record(h2d_s)
+        main.wait_event(ev_drained[s_])                 # output set s_ (written two steps ago) is back on the host
         for c in range(n_chunks):
-            main.wait_event(ev_in[c])
-            chunk_graphs[c].replay()
-            ev_out[c].record(main)
-        ev_step.record(main)
+            main.wait_event(ev_in[s_][c])
+            chunk_graphs[s_][c].replay()
+            ev_out[s_][c].record(main)
+        ev_consumed[s_].record(main)
         with torch.cuda.stream(d2h_s):
             for c, (lo, hi) in enumerate(bounds):
-                d2h_s.wait_event(ev_out[c])
-                out_host[lo:hi].copy_(out_view[lo:hi], non_blocking=True)
-        main.wait_stream(d2h_s)
+                d2h_s.wait_event(ev_out[s_][c])
+                out_host[lo:hi].copy_(out_views[s_][lo:hi], non_blocking=True)
+            ev_drained[s_].record(d2h_s)
 
-    ev_step.record(main)
+    for e_ in ev_consumed + ev_drained:
+        e_.record(main)
     for _ in range(max(3, args.warmup)):
         e2e_step()
     sync_all()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
-    torch.cuda.synchronize()
+    torch.cuda.synchronize()                     # includes the last step's device->host copies
     e2e_s = time.perf_counter() - t0
     sync_all()
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -498,7 +507,7 @@ def run_b200_arm(args):
     splits_used = num_splits or b200ops.decode_num_splits(B, Hkv_l, per_seq * page, b200ops.sm_count(dev))
 
     # ---- free the headline's memory before the auxiliary figures
-    del graph, chunk_graphs, mgr, qkv_dev, out_dev, out_view, qkv_host, out_host, block_table, seqlens
+    del graph, chunk_graphs, mgr, qkv_dev, out_dev, qkv_devs, out_devs, out_views, qkv_host, out_host, block_table, seqlens
     _release()
 
     peak, peak_tf, peak_src = measured_peaks()
@@ -582,7 +591,7 @@ def run_b200_arm(args):
                                    f"cache [n_blocks,256,{Hkv_l},{D}] per rank, replicated block tables, "
                                    "no collective inside attention (core/engine.py:108-114)"),
                    "num_splits": splits_used, "variant": args.variant, "pdl": args.pdl,
-                   "e2e_pipeline": f"{n_chunks} chunks of {L // n_chunks} layers, H2D/D2H on side streams"},
+                   "e2e_pipeline": f"{n_chunks} chunks of {L // n_chunks} layers, H2D/D2H on side streams, two alternating device-side step buffers"},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": UNIT,
                      "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
                      "kernel": "paged_decode_kernel", "kernel_us": round(kernel_us, 3),

@@ -69,24 +69,28 @@ def test_split_counts(num_splits):
 @pytest.mark.parametrize("num_splits", [2, 4, 5, 8])
 def test_cluster_merge_equals_workspace_merge(num_splits, Hq, Hkv, D):
     """Split counts 2..8 merge the splits of a segment through distributed shared memory (one thread-block cluster per
-    segment); the workspace + last-arriver form does the same arithmetic in the same order: bit-identical outputs and
-    lse, with empty splits (short rows) and every variant's shared-memory layout."""
+    segment); the workspace + last-arriver form does the same arithmetic except for the order in which the split
+    weights are summed (sequential here, a warp-shuffle tree there): outputs within one bf16 ulp (and almost all
+    bit-identical), lse to fp32 rounding — with empty splits (short rows) and every variant's shared-memory layout."""
     lens = [4095, 3000, 257, 5, 0, 2047, 2048, 1023, 64, 1]
     case = make_paged_case(len(lens), Hq, Hkv, D, lens, seed=num_splits * 7 + Hq)
-    a = check(case, num_splits=num_splits, cluster_merge=True)
-    b = check(case, num_splits=num_splits, cluster_merge=False)
-    assert torch.equal(a, b)
+
+    def same(a, b, what):
+        assert int(bf16_ulp_diff(a.cpu(), b.cpu()).max()) <= 1, what
+        assert float((a == b).float().mean()) > 0.999, what
+
+    same(check(case, num_splits=num_splits, cluster_merge=True), check(case, num_splits=num_splits, cluster_merge=False),
+         "default variant")
     for v in ([1, 5, 8] if D == 128 else [2]):
-        a = check(case, num_splits=num_splits, variant=v, cluster_merge=True)
-        b = check(case, num_splits=num_splits, variant=v, cluster_merge=False)
-        assert torch.equal(a, b), f"variant {v}"
+        same(check(case, num_splits=num_splits, variant=v, cluster_merge=True),
+             check(case, num_splits=num_splits, variant=v, cluster_merge=False), f"variant {v}")
     d = to_dev(case)
     lse = [torch.empty(len(lens) * Hq, dtype=torch.float32, device="cuda") for _ in range(2)]
     for i, cm in enumerate((True, False)):
         b200ops.paged_attn_decode(d["q"][:, 0], d["k_cache"].clone(), d["v_cache"].clone(), d["k"][:, 0], d["v"][:, 0],
                                   d["cos"], d["sin"], d["seqlens"], d["table"], softmax_scale=case["scale"],
                                   softmax_lse=lse[i], num_splits=num_splits, cluster_merge=cm)
-    assert torch.equal(lse[0], lse[1])
+    assert torch.allclose(lse[0], lse[1], rtol=2e-6, atol=2e-6)
 
 
 @pytest.mark.parametrize("D,variants", [(128, [1, 2, 3, 4, 5, 6, 7, 8]), (64, [1, 2, 3])])
