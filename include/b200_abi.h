@@ -400,8 +400,8 @@ void b200_debug_prefill_trace(void* dev_buf);
  * previous kernel of the stream; it waits for that kernel before reading x / residual).  Every form also releases a
  * PDL-launched SUCCESSOR at its start, so a weight-streaming GEMM behind it fetches weights during the exchange. */
 #define B200_AR_FLAG_PDL 0x100
-/* OR-ed into `mode` with B200_AR_MODE_NVLS: the owner sends y as 16-byte flag-in-data packets (multimem.st into every
- * rank's y staging, the LL form's region: rows * n * 4 bytes) and every rank unpacks its local copy into `y` (any local
+/* OR-ed into `mode` with B200_AR_MODE_NVLS: the owner sends y as 16-byte flag-in-data packets (plain peer stores into
+ * every rank's y staging, ystage_peers[], the LL form's region: rows * n * 4 bytes) and every rank unpacks its local copy into `y` (any local
  * tensor) — one one-way hop instead of a release fence + a counter round trip.  epoch must hold MAX_CTAS + 11 words. */
 #define B200_AR_FLAG_PACKET_TAIL 0x200
 
@@ -429,7 +429,7 @@ typedef struct b200_ar_args {
     const void* x_mc;         /* NVLS form: multicast address of the x slot (same offset as x_peers[rank])            */
     void*       y_mc;         /* NVLS form: multicast address of the y buffer (same offset as y)                      */
     void*       flags_mc;     /* NVLS form: multicast address of the flag region (same offset as flag_peers[rank])    */
-    void*       ystage_mc;    /* NVLS form + B200_AR_FLAG_PACKET_TAIL: multicast address of the y staging             */
+    void*       ystage_mc;    /* reserved (multicast address of the y staging; unused: unicast packets are faster)    */
 } b200_ar_args;
 
 /* Row-sharded ("two-shot") form for world > 1, rows <= B200_AR_MAX_CTAS: rank r OWNS rows

@@ -329,8 +329,8 @@ class PeerComm:
             if packet_tail:                 # y travels as flag-in-data packets through the y staging; y itself is local
                 assert rows * n * 4 <= 2 * self.slot_bytes
                 a.mode |= _lib.AR_FLAG_PACKET_TAIL
-                a.ystage_mc = self._mc_base + self._ystage_off
-                a.ystage_peers[self.rank] = self._base + self._ystage_off
+                for r in range(self.world):
+                    a.ystage_peers[r] = self._peer_base[r] + self._ystage_off
         if nvls1:
             assert self.has_multicast, "PeerComm: the NVLS forms need a multicast mapping (symm back end on an NVSwitch node)"
             a.mode = _lib.AR_MODE_NVLS_ONEHOP

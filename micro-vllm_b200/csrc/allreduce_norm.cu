@@ -470,8 +470,11 @@ __device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
     return r;
 }
+// WEAK multicast store: fire-and-forget like the LL form's packets (a relaxed.sys store makes the issuing thread wait
+// for the NVLink round trip; the data is published either by the release that follows the CTA barrier or by the flag
+// words inside the packet itself)
 __device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};"
                  :: "l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
@@ -484,8 +487,8 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // per requester — 1 MB per GPU at decode sizes, far below NVLink bandwidth), adds its REPLICATED residual, normalises
 // and stores y locally.  No second hop and no trailing barrier: like the one-shot peer-load form, consecutive calls
 // must alternate x slots, and res_out / residual are full tensors on every rank.
-// PKT = the two-hop form with a PACKET tail: the owner multimem.st's y as 16-byte packets {d0, e, d1, e} (e = call
-// counter) into every rank's y staging, and every rank's CTAs poll their LOCAL staging and unpack it into the plain y.
+// PKT = the two-hop form with a PACKET tail: the owner stores y as 16-byte packets {d0, e, d1, e} (e = call counter)
+// into every rank's y staging with plain peer stores, and every rank's CTAs poll their LOCAL staging and unpack it into the plain y.
 // That replaces "multimem.red.release per CTA (a system-scope fence behind 16 KB of multicast stores) + wait for all
 // 8 x grid arrivals" — 6.7 us of the 16.4 us kernel at 8 ranks (profiles/r02/allreduce_tp8.json) — by one one-way hop.
 template <int VPT, typename WT, bool ONE, bool PKT>
@@ -578,9 +581,17 @@ allreduce_nvls_kernel(const __grid_constant__ ArParams p, const int world) {
                 if constexpr (ONE) {
                     st_na_v4(p.y + row * p.sy + (int64_t)v * 8, o);
                 } else if constexpr (PKT) {
-                    uint8_t* dst = p.ystage_mc + (size_t)row * row_stage + (size_t)v * 32;
-                    multimem_st_v4(dst, make_uint4(o.x, pkt_e, o.y, pkt_e));
-                    multimem_st_v4(dst + 16, make_uint4(o.z, pkt_e, o.w, pkt_e));
+                    // unicast packets to every rank (own copy included): measured on B200s, multicast stores need ~6 us
+                    // to land on every GPU, plain peer stores of the LL form ~1 us (profiles/r02/allreduce_tp2.json)
+                    const size_t off = (size_t)row * row_stage + (size_t)v * 32;
+#pragma unroll
+                    for (int k = 0; k < B200_AR_MAX_WORLD; ++k) {
+                        if (k < world) {
+                            uint8_t* dst = p.ystage[(k + p.rank) % world] + off;
+                            st_ll(dst, o.x, o.y, pkt_e);
+                            st_ll(dst + 16, o.z, o.w, pkt_e);
+                        }
+                    }
                 } else {
                     multimem_st_v4(p.y_mc + row * p.sy + (int64_t)v * 8, o);  // lands in every rank's y buffer
                 }
@@ -885,10 +896,11 @@ extern "C" int b200_allreduce_residual_rmsnorm(const b200_ar_args* a, void* stre
         B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
     }
     if (nvls && (a->mode & B200_AR_FLAG_PACKET_TAIL)) {
-        if (!a->ystage_mc || !aligned16(a->ystage_mc) || !a->ystage_peers[a->rank] || !aligned16(a->ystage_peers[a->rank]))
-            B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: the packet tail needs ystage_mc and ystage_peers[rank]");
-        p.ystage_mc = (uint8_t*)a->ystage_mc;
-        p.ystage[a->rank] = (uint8_t*)a->ystage_peers[a->rank];
+        for (int r = 0; r < a->world; ++r) {
+            if (!a->ystage_peers[r] || !aligned16(a->ystage_peers[r]))
+                B200_FAIL(B200_E_NULL, "allreduce_residual_rmsnorm: the packet tail needs ystage_peers[%d]", r);
+            p.ystage[r] = (uint8_t*)a->ystage_peers[r];
+        }
         if (a->w_dtype == B200_DT_F32) return launch_nvls<float, false, true>(p, a->world, st);
         if (a->w_dtype == B200_DT_BF16) return launch_nvls<__nv_bfloat16, false, true>(p, a->world, st);
         B200_FAIL(B200_E_UNSUPPORTED, "allreduce_residual_rmsnorm: weight dtype %d", a->w_dtype);
