@@ -83,7 +83,7 @@ def test_argument_errors_without_device():
     assert lib.b200_paged_attn_decode(ctypes.byref(a), None) == _lib.E_RANGE       # num_splits
     assert lib.b200_decode_workspace_bytes(32, 32, 8, 128, 4) == 65536 * 4 + 32 * 32 * 4 * 4 + 32 * 32 * 4 * 128 * 4
     assert lib.b200_decode_workspace_bytes(32, 30, 8, 128, 4) == -1
-    assert lib.b200_prefill_workspace_bytes(2, 128, 32, 128) == 2 * 128 * 32 * 128 * 2
+    assert lib.b200_prefill_workspace_bytes(2, 128, 32, 128) == 2 * 128 * 32 * 128 * 2 + 256   # rotated Q + work counter
 
 
 def test_allreduce_norm_argument_errors_without_device():

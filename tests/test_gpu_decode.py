@@ -76,7 +76,14 @@ def test_cluster_merge_equals_workspace_merge(num_splits, Hq, Hkv, D):
     case = make_paged_case(len(lens), Hq, Hkv, D, lens, seed=num_splits * 7 + Hq)
 
     def same(a, b, what):
-        assert int(bf16_ulp_diff(a.cpu(), b.cpu()).max()) <= 1, what
+        # one bf16 ulp, except on elements that cancel to ~0 (|value| below 2^-20 of the tensor's scale), where the
+        # fp32 re-association noise of the split weights spans several (tiny) bf16 ulps: bound those absolutely
+        a, b = a.cpu(), b.cpu()
+        ulp = bf16_ulp_diff(a, b)
+        absd = (a.float() - b.float()).abs()
+        floor = 2.0 ** -20 * max(1.0, float(a.float().abs().max()))
+        bad = (ulp > 1) & (absd > floor)
+        assert int(bad.sum()) == 0, (what, int(ulp.max()), float(absd[bad].max()))
         assert float((a == b).float().mean()) > 0.999, what
 
     same(check(case, num_splits=num_splits, cluster_merge=True), check(case, num_splits=num_splits, cluster_merge=False),

@@ -103,6 +103,60 @@ def test_prefill_two_tiles_long_and_noncausal(variant):
     check_prefill(make_paged_case(2, 3, 3, 64, [5, 130], S_new=260, seed=54), causal=False, variant=variant)
 
 
+PERSIST_CASES = [  # B, S, Hq, Hkv, D, prefixes, causal   (work items of the persistent kernel >> 148 CTAs)
+    (3, 700, 32, 8, 128, [0, 131, 300], True),               # 288 items, 6..8 KV tiles, ragged prefixes
+    (40, 100, 8, 2, 128, [(i * 37) % 90 for i in range(40)], True),   # 160 items of ONE or TWO KV tiles each
+    (6, 520, 14, 2, 64, [0, 1, 255, 256, 77, 600], True),    # G = 7: row-tile pairs, dead second tile, D = 64
+    (5, 260, 32, 8, 128, [5, 130, 0, 256, 300], False),      # non-causal, partial last tile (V tail zeroing)
+    (2, 1500, 32, 8, 128, [0, 40], True),                    # 384 items, up to 13 KV tiles: several items per CTA
+]
+
+
+@pytest.mark.parametrize("variant", [0, 9, 10, 11])
+@pytest.mark.parametrize("B,S,Hq,Hkv,D,prefixes,causal", PERSIST_CASES)
+def test_prefill_persistent_many_items(variant, B, S, Hq, Hkv, D, prefixes, causal):
+    """variants 9..11 (and the default, which selects 9 for these sizes) = ONE resident CTA per SM pulling
+    (query-tile pair) work items from a device counter: every mbarrier phase keeps counting across items, the next
+    item's Q / K / V loads and first Q.K^T overlap the previous item's last softmax and epilogue."""
+    if variant in (10, 11) and S > 700:
+        pytest.skip("softmax-arithmetic variants are covered on the smaller cases")
+    check_prefill(make_paged_case(B, Hq, Hkv, D, prefixes, S_new=S, seed=S + Hq + variant), causal=causal,
+                  variant=variant)
+
+
+@pytest.mark.parametrize("B,S,Hq,Hkv,D,prefixes", PAIR_CASES)
+def test_prefill_persistent_few_items(B, S, Hq, Hkv, D, prefixes):
+    """Fewer items than SMs: every CTA runs one item and then meets the end-of-work sentinel."""
+    check_prefill(make_paged_case(B, Hq, Hkv, D, prefixes, S_new=S, seed=S + Hq + 9), variant=9)
+
+
+def test_prefill_persistent_counter_rearmed_every_call():
+    """The work-item counter lives in the call's workspace and is zeroed by the RoPE/append kernel of the SAME call:
+    back-to-back calls and CUDA-graph replays must each see a fresh counter (a stale one would skip all work)."""
+    case = make_paged_case(3, 32, 8, 128, [0, 131, 300], S_new=700, seed=77)
+    first = check_prefill(case)
+    d = to_dev(case)
+    args = (d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"], d["cos"], d["sin"], d["seqlens"], d["table"])
+    out = torch.empty_like(d["q"])
+    for _ in range(3):
+        out.zero_()
+        b200ops.paged_attn_prefill(*args, softmax_scale=case["scale"], out=out)
+        assert torch.equal(out, first)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        b200ops.paged_attn_prefill(*args, softmax_scale=case["scale"], out=out)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        b200ops.paged_attn_prefill(*args, softmax_scale=case["scale"], out=out)
+    for _ in range(3):
+        out.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, first)
+
+
 def test_prefill_interleaved_and_noncausal():
     case = make_paged_case(2, 8, 4, 128, [0, 130], S_new=140, seed=3)
     check_prefill(case, interleaved=True)
@@ -156,7 +210,7 @@ def test_prefill_then_decode_consistency():
     assert_close(last, full[:, S].float(), what="decode vs last prefill row")
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 6])
+@pytest.mark.parametrize("variant", [0, 1, 2, 6, 9])
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
 def test_prefill_poisoned_cache_tail(variant, D, Hq, Hkv):
     """never-written cache slots may hold NaN / Inf (torch.empty caches, recycled pages).  Keys at or

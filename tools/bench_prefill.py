@@ -18,6 +18,9 @@ CASES = [  # name, B, S, prefix, Hq, Hkv, D
     ("l8_b1_s2048_p6144", 1, 2048, 6144, 32, 8, 128),
     ("q7_b2_s4096", 2, 4096, 0, 28, 4, 128),
     ("q05_b4_s2048", 4, 2048, 0, 14, 2, 64),
+    ("l8_b4_s512", 4, 512, 0, 32, 8, 128),
+    ("l8_b8_s1024", 8, 1024, 0, 32, 8, 128),
+    ("q7_b1_s2048", 1, 2048, 0, 28, 4, 128),
 ]
 
 
@@ -68,7 +71,7 @@ def main():
         ms1 = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=1))
         rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), graph_ms=round(ms_graph, 4),
                    graph_tflops=round(flops / ms_graph / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
-        for var, key in ((3, "sm_packed"), (4, "sm_poly25"), (5, "sm_poly50"), (6, "pair_poly25"), (7, "pair_packed"), (8, "pair_poly50")):
+        for var, key in ((4, "sm_poly25"), (6, "pair_poly25"), (9, "persist_poly25"), (10, "persist_packed"), (11, "persist_poly50")):
             msv = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=var))
             rec[key + "_tflops"] = round(flops / msv / 1e9, 1)
         if fa is not None:

@@ -64,7 +64,9 @@ summ = {
     "QK_issue_lead_over_softmax_start": avg(lambda j: r["sm_tile_top"][j] - r["mma_QK_issue"][j]),
     "K_issue_lead_over_QK_issue": avg(lambda j: r["mma_QK_issue"][j] - r["tma_K_issue"][j]),
 }
-print(json.dumps({"variant": variant, "S": S, "tiles": nt, "steady_state_clk": summ}))
+item_ends = [int(x) - t0 for x in t[12].tolist() if int(x) != 0]
+print(json.dumps({"variant": variant, "S": S, "tiles": nt, "steady_state_clk": summ,
+                  "cta0_item_epilogue_done_clk": item_ends}))
 for j in list(range(0, min(6, nt))) + list(range(max(6, nt - 3), nt)):
     print(j, {kk: vv[j] for kk, vv in rel.items()})
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
