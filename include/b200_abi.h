@@ -335,7 +335,7 @@ typedef struct b200_prefill_args {
     const int32_t* cache_seqlens; /* [B] prefix lengths P_b                 */
     const int32_t* block_table;   /* [B, max_blocks_per_seq]                */
     void*       out;          /* [B, S, Hq, D] bf16 */
-    void*       workspace;    /* b200_prefill_workspace_bytes: rotated Q    */
+    void*       workspace;    /* b200_prefill_workspace_bytes: rotated Q + the attention kernel's work-item counter */
     int64_t     workspace_bytes;
     int32_t B, S, Hq, Hkv, D;
     int32_t rotary_dim, rotary_interleaved, rot_rows;

@@ -115,11 +115,16 @@ struct AppendParams {
     int n_blocks, block_size, max_blocks_per_seq;
     int64_t q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh;
     int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
+    int* work_counter;     // work-item counter of the persistent attention kernel that follows: zeroed here
 };
 
 __global__ void __launch_bounds__(128)
 prefill_rope_append_kernel(const __grid_constant__ AppendParams p) {
     const int s = blockIdx.x, b = blockIdx.y;
+    // the persistent attention kernel is launched with programmatic stream serialization: its CTAs may take their SMs,
+    // set up barriers / TMEM / descriptors and then sit in griddepcontrol.wait while this grid is still running
+    pdl_release_next();
+    if (s == 0 && b == 0 && threadIdx.x == 0 && p.work_counter != nullptr) *p.work_counter = 0;
     const int D = p.D, JB = D / 16, CPR = D / 8;
     const int pos = __ldg(p.seqlens + b) + s;
     const int rd = p.cos ? p.rotary_dim : 0;
@@ -1136,6 +1141,485 @@ prefill_attn_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     }
 }
 
+// ------------------------------------------------------------------ kernel 2d: persistent pair kernel
+// The pair kernel above pays ~16 000 clk per CTA outside its steady-state loop (measured: ncu sm__cycles_active x 148
+// minus tiles x 3356 clk, the same figure at S = 512, 2048 and 8192 — profiles/r02/prefill_small_r02.md): CTA launch
+// behind the previous CTA's exit, barrier init, tcgen05.alloc behind the previous dealloc, descriptor fetch, Q load
+// latency, pipeline fill, drain and the epilogue with the tensor pipe idle.  At the reference's prompt sizes (<= 2048
+// tokens, engine.py:45) a CTA has 1..16 KV tiles, so that fixed cost was 40-60 % of the kernel.
+// Here ONE CTA PER SM stays resident and pulls work items (the same pair of 128-row query tiles, in the same
+// longest-first order) from a device counter that kernel 1 zeroes:
+//   * TMEM, mbarriers and descriptors are set up once per SM; every mbarrier phase runs on a tile counter that keeps
+//     counting across items, so the K/V ring never drains between items: the producer is already loading the next
+//     item's Q (single buffer, released by a tcgen05.commit behind the item's last Q.K^T) and K/V tiles while the
+//     softmax warps finish the previous item's last tile and epilogue;
+//   * the next item's first Q.K^T is issued right behind the last P.V of the current item (in-order tensor pipe:
+//     it may overwrite S/P), and its first P.V — the first write to O — is ordered behind the epilogue's tcgen05.ld
+//     of O by the softmax warps themselves (same threads: epilogue, then the next item's first tile);
+//   * dynamic pull (one atomicAdd per item by the producer behind the item's last tile loads, published with the prefix length
+//     through an 8-slot shared-memory ring + mbarrier) keeps the longest-first list balanced like the hardware CTA
+//     scheduler did.
+template <int D_>
+struct PCfg4 : PCfg3<D_> {
+    using Base = PCfg3<D_>;
+    static constexpr int NBARS = 32;
+    static constexpr int NSLOT = 8;
+    static constexpr int OFF_XCH = Base::OFF_BAR + NBARS * 8 + 16;           // row max exchange [2 tiles][2][2][128] f32
+    static constexpr int OFF_LX = OFF_XCH + 2 * 2 * 2 * 128 * 4;             // row sum exchange [2 tiles][2][128] f32
+    static constexpr int OFF_ITEM = OFF_LX + 2 * 2 * 128 * 4;                // item ring [NSLOT] {id, prefix}
+    static constexpr int OFF_STG = OFF_ITEM + NSLOT * 8;                     // epilogue staging: 16 warps x [16 rows][64 B]
+    static constexpr int SMEM = OFF_STG + 16 * 1024 + 1024;
+};
+enum { B4_QE = 15, B4_IF = 16 };
+
+struct PersistParams {
+    PrefillParams p;
+    int pair_heads;
+    int total;             // work items = nx * ny * B
+    int* counter;          // zeroed by prefill_rope_append_kernel of the same call
+};
+
+template <class C, int SM>
+__global__ void __launch_bounds__(C::THREADS, 1)
+prefill_attn_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                            const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ PersistParams pp) {
+    constexpr int D = C::D;
+    const PrefillParams& p = pp.p;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_u32 = smem_u32(smem_raw);
+    const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw_u32);
+    const uint32_t sQ = base + C::OFF_Q, sK = base + C::OFF_K, sV = base + C::OFF_V;
+    const uint32_t bars = base + C::OFF_BAR;
+    auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
+    volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
+    volatile int* s_item = reinterpret_cast<volatile int*>(smem + C::OFF_ITEM);
+    const int total = pp.total;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        mbar_init(bar(B3_Q), 1);
+        mbar_init(bar(B4_QE), 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bar(B3_KF + s), 1); mbar_init(bar(B3_KE + s), 1);
+            mbar_init(bar(B3_VF + s), 1); mbar_init(bar(B3_VE + s), 1);
+            mbar_init(bar(B3_SF + s), 1); mbar_init(bar(B3_PF + s), C::GROUP_THREADS); mbar_init(bar(B3_PD + s), 1);
+        }
+        for (int s = 0; s < C::NSLOT; ++s) mbar_init(bar(B4_IF + s), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32((const void*)s_tmem)), "r"((uint32_t)C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+    // everything above overlapped the tail of prefill_rope_append_kernel (PDL); everything below reads what it wrote
+    // (work counter, rotated Q, K/V pages) or writes `out`
+    pdl_wait_prev();
+
+    // one work item: the pair of query tiles of prefill_attn_pair_kernel, same longest-first numbering
+    struct Item { int b, hq0, hq1, q00, q01, q01_load, kvh, prefix, seqlen_k, n_tiles; };
+    auto decode = [&](int id, int prefix) {
+        Item I;
+        const int by = id % p.ny;
+        const int xb = id / p.ny;
+        I.b = xb % p.B;
+        const int xt = p.nx - 1 - xb / p.B;
+        I.hq0 = pp.pair_heads ? 2 * by : by;
+        I.hq1 = pp.pair_heads ? I.hq0 + 1 : I.hq0;
+        I.q00 = pp.pair_heads ? xt * C::BM : 2 * xt * C::BM;
+        I.q01 = pp.pair_heads ? I.q00 : I.q00 + C::BM;
+        I.q01_load = (I.q01 < p.S) ? I.q01 : I.q00;
+        I.kvh = I.hq0 / p.G;
+        I.prefix = prefix;
+        I.seqlen_k = prefix + p.S;
+        const int kv_end = p.causal ? min(I.seqlen_k, prefix + I.q01 + C::BM) : I.seqlen_k;
+        I.n_tiles = (kv_end + C::BN - 1) / C::BN;
+        return I;
+    };
+    // consumers: wait for item number `it` of this CTA; false = no more work
+    auto next_item = [&](int it, Item& I) {
+        const int slot = it % C::NSLOT;
+        mbar_wait(bar(B4_IF + slot), (uint32_t)(it / C::NSLOT) & 1u);
+        const int id = s_item[2 * slot], prefix = s_item[2 * slot + 1];
+        if (id >= total) return false;
+        I = decode(id, prefix);
+        return true;
+    };
+
+    if (warp == 0) {
+        // ===================================================== scheduler + TMA producer
+        int nid = 0, npf = 0;
+        auto fetch = [&]() {
+            int v = 0, pf = 0;
+            if (lane == 0) {
+                v = atomicAdd(pp.counter, 1);
+                if (v < total) pf = __ldg(p.seqlens + (v / p.ny) % p.B);
+            }
+            nid = __shfl_sync(0xffffffffu, v, 0);
+            npf = __shfl_sync(0xffffffffu, pf, 0);
+        };
+        auto publish = [&](int it) {
+            if (lane == 0) {
+                const int slot = it % C::NSLOT;
+                s_item[2 * slot] = nid; s_item[2 * slot + 1] = npf;
+                mbar_arrive(bar(B4_IF + slot));                       // release: the slot is visible to the waiters
+            }
+            __syncwarp();
+        };
+        fetch();
+        publish(0);
+        uint32_t g = 0;                                               // K/V tiles issued so far (all items)
+        for (int it = 0; nid < total; ++it) {
+            const Item I = decode(nid, npf);
+            mbar_wait(bar(B4_QE), (uint32_t)(it & 1) ^ 1u);           // previous item's last Q.K^T has read Q
+            if (elect_one()) {
+                mbar_expect_tx(bar(B3_Q), 2 * C::TILE_B);
+#pragma unroll
+                for (int sl = 0; sl < C::DSLABS; ++sl) {
+                    tma_load_4d(sQ + sl * C::SLAB_B, &tm_q, bar(B3_Q), sl * 64, I.hq0, I.q00, I.b);
+                    tma_load_4d(sQ + C::TILE_B + sl * C::SLAB_B, &tm_q, bar(B3_Q), sl * 64, I.hq1, I.q01_load, I.b);
+                }
+            }
+            __syncwarp();
+            const int32_t* bt = p.block_table + (int64_t)I.b * p.bt_sb;
+            const int j_pull = max(0, I.n_tiles - 3);
+            for (int j = 0; j < I.n_tiles; ++j, ++g) {
+                const int st = (int)(g & 1u);
+                const uint32_t ph = (g >> 1) & 1u;
+                const int n0 = j * C::BN;
+                const int pe = n0 / p.block_size;
+                int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : 0;
+                if (page < 0 || page >= p.n_blocks) page = 0;          // memory safety; tokens are masked or undefined
+                const int tok = n0 - pe * p.block_size;
+                mbar_wait(bar(B3_KE + st), ph ^ 1u);
+                pf_stamp(p, lane == 0 && it == 0, 9, j);
+                if (elect_one()) {
+                    mbar_expect_tx(bar(B3_KF + st), C::TILE_B);
+#pragma unroll
+                    for (int sl = 0; sl < C::DSLABS; ++sl)
+                        tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(B3_KF + st), sl * 64, I.kvh, tok, page);
+                }
+                __syncwarp();
+                mbar_wait(bar(B3_VE + st), ph ^ 1u);
+                pf_stamp(p, lane == 0 && it == 0, 10, j);
+                if (elect_one()) {
+                    mbar_expect_tx(bar(B3_VF + st), C::TILE_B);
+#pragma unroll
+                    for (int sl = 0; sl < C::DSLABS; ++sl)
+                        tma_load_4d(sV + st * C::TILE_B + sl * C::SLAB_B, &tm_v, bar(B3_VF + st), sl * 64, I.kvh, tok, page);
+                }
+                __syncwarp();
+                if (j == j_pull) {
+                    // Pull the next item (behind this tile's loads) three tiles before the end of this one: late enough that the list stays a
+                    // DYNAMIC longest-first queue (pulling at the start of every item hands each CTA its first two items
+                    // at launch — a static round-robin split, measured 63 us instead of 48 us at S = 2048 with 256 items
+                    // on 148 SMs), early enough that the atomic, the next Q load and its first Q.K^T hide behind this
+                    // item's remaining tiles; items of <= 3 tiles (the end of the list) pull at once.
+                    fetch();
+                    publish(it + 1);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer (whole warp waits, one elected lane issues)
+        constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q K-major (smem), B=K K-major
+        constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P (TMEM), B=V MN-major
+        bool trace_it = true;
+        // gj = tile number over all items (barrier stages / phases); `last` = the item's last tile: Q is free behind it
+        auto issue_qk = [&](int t, uint32_t gj, int j, bool last) {
+            const uint32_t k_base = sK + (gj & 1u) * C::TILE_B;
+            const uint32_t q_base = sQ + t * C::TILE_B;
+            const uint32_t s_tm = tmem + C::TM_S + t * 128;
+            pf_stamp(p, lane == 0 && t == 0 && trace_it, 6, j);
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t da = umma_desc_sw128(q_base + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    const uint64_t db = umma_desc_sw128(k_base + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
+                    umma_bf16(s_tm, da, db, IDESC_QK, k > 0 ? 1u : 0u);
+                }
+                tc_commit(bar(B3_SF + t));
+                if (t == 1) {
+                    tc_commit(bar(B3_KE + (gj & 1u)));                // both tiles have consumed K_j
+                    if (last) tc_commit(bar(B4_QE));                  // ... and nobody reads Q of this item any more
+                }
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int t, uint32_t gj, int j) {              // O_t += P_t . V_j ; waits for tile t's softmax
+            pf_stamp(p, lane == 0 && t == 0 && trace_it, 7, j);
+            mbar_wait(bar(B3_PF + t), gj & 1u);
+            pf_stamp(p, lane == 0 && t == 0 && trace_it, 8, j);
+            tc_fence_after();
+            const uint32_t v_base = sV + (gj & 1u) * C::TILE_B;
+            const uint32_t p_tm = tmem + C::TM_S + t * 128;            // P overwrote S in place
+            const uint32_t o_tm = tmem + C::TM_O + t * 128;
+            const uint32_t first = (j > 0) ? 1u : 0u;
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < C::BN / 16; ++k) {
+                    const uint64_t db = umma_desc_sw128(v_base + k * 2048, C::SLAB_B, 1024);
+                    umma_bf16_ts(o_tm, p_tm + (k < 4 ? k * 8 : 64 + (k - 4) * 8), db, IDESC_PV, k > 0 ? 1u : first);
+                }
+                tc_commit(bar(B3_PD + t));
+                if (t == 1) tc_commit(bar(B3_VE + (gj & 1u)));         // both tiles have consumed V_j
+            }
+            __syncwarp();
+        };
+        uint32_t g = 0;
+        Item I;
+        for (int it = 0; next_item(it, I); ++it) {
+            trace_it = (it == 0);
+            const int n_tiles = I.n_tiles;
+            mbar_wait(bar(B3_Q), (uint32_t)it & 1u);
+            mbar_wait(bar(B3_KF + (g & 1u)), (g >> 1) & 1u);
+            tc_fence_after();
+            issue_qk(0, g, 0, n_tiles == 1);
+            issue_qk(1, g, 0, n_tiles == 1);
+            for (int j = 0; j < n_tiles; ++j) {
+                const uint32_t gj = g + (uint32_t)j;
+                const bool more = (j + 1 < n_tiles);
+                mbar_wait(bar(B3_VF + (gj & 1u)), (gj >> 1) & 1u);
+                if (!more && I.seqlen_k - j * C::BN < C::BN) {
+                    zero_v_tail<C::DSLABS>(sV + (gj & 1u) * C::TILE_B, I.seqlen_k - j * C::BN, lane, 32);
+                    __syncwarp();
+                }
+                if (more) mbar_wait(bar(B3_KF + ((gj + 1u) & 1u)), ((gj + 1u) >> 1) & 1u);
+                issue_pv(0, gj, j);
+                if (more) issue_qk(0, gj + 1u, j + 1, j + 2 == n_tiles);
+                issue_pv(1, gj, j);
+                if (more) issue_qk(1, gj + 1u, j + 1, j + 2 == n_tiles);
+            }
+            g += (uint32_t)n_tiles;
+        }
+    } else {
+        // ===================================================== softmax / correction / epilogue (see the pair kernel)
+        const int w = warp - 2;
+        const int t = w >> 3;                                  // which Q tile
+        const int half = (w >> 2) & 1;                         // which 64 key columns / which half of D
+        const int quarter = warp & 3;                          // TMEM lane quarter this warp may access
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const float sl2 = p.scale_log2;
+        constexpr int HC = C::BN / 2, HD = D / 2;
+        const uint32_t ts = tmem + lane_sel + C::TM_S + t * 128 + half * HC;     // my 64 score columns; my P words
+        const uint32_t to = tmem + lane_sel + C::TM_O + t * 128 + half * HD;     // overwrite their first 32
+        constexpr int NPOLY = SM > 0 ? SM - 1 : 0;
+        volatile float* xch = reinterpret_cast<volatile float*>(smem + C::OFF_XCH) + t * 512;   // [parity][half][row]
+        volatile float* lx = reinterpret_cast<volatile float*>(smem + C::OFF_LX) + t * 256;     // [half][row]
+        const int pair_bar = 1 + t * 4 + quarter;              // named barrier of the 2 warps that share these rows
+        uint32_t g = 0;
+        Item I;
+        for (int it = 0; next_item(it, I); ++it) {
+            const int hq = t ? I.hq1 : I.hq0;
+            const int q0 = t ? I.q01 : I.q00;
+            const int prefix = I.prefix, seqlen_k = I.seqlen_k, n_tiles = I.n_tiles;
+            const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
+            // smallest / largest query position of this warp's 32 rows: a 32-key chunk is DEAD for the whole warp when it
+            // starts beyond qhi (all probabilities are exact zeros: no tcgen05.ld, no exponentials), needs the mask when
+            // it reaches beyond qlo, and takes the unmasked fast path otherwise.  On a diagonal tile that is 6 dead,
+            // 4 masked and 6 plain chunks of 16 instead of 16 masked ones (the diagonal tile took 5600 clk, a plain one
+            // 3350: profiles/r02/trace_prefill_s2048_pair_before.log).
+            const int qlo = p.causal ? (prefix + q0 + quarter * 32) : 0x3fffffff;     // qhi = qlo + 31
+            float m_ref = -CUDART_INF_F, l = 0.0f;
+            for (int j = 0; j < n_tiles; ++j) {
+                const uint32_t gj = g + (uint32_t)j;
+                const int n0 = j * C::BN + half * HC;
+                const bool tr = (tid == 64) && it == 0;
+                pf_stamp(p, tr, 11, j);
+                mbar_wait(bar(B3_SF + t), gj & 1u);
+                pf_stamp(p, tr, 0, j);
+                pf_stamp(p, tr, 1, j);
+                tc_fence_after();
+                // warp-uniform: a tile with no chunk reaching beyond qlo / seqlen_k takes the straight-line code
+                const bool plain = !((n0 + HC - 1 > qlo) || (n0 + HC > seqlen_k));
+                float m4[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+                if (plain) {
+#pragma unroll
+                    for (int c = 0; c < HC / 32; ++c) {
+                        uint32_t r[32];
+                        tmem_ld32(ts + c * 32, r);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                m4[u] = fmaxf(fmaxf(m4[u], __uint_as_float(r[i + u])), __uint_as_float(r[i + 4 + u]));
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < HC / 32; ++c) {
+                        const int c0 = n0 + c * 32;
+                        if ((c0 > qlo + 31) || (c0 >= seqlen_k)) continue;            // dead chunk
+                        uint32_t r[32];
+                        tmem_ld32(ts + c * 32, r);
+                        tmem_wait_ld();
+                        if ((c0 + 31 > qlo) || (c0 + 32 > seqlen_k)) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const int tok = n0 + c * 32 + i;
+                                if (tok > qpos || tok >= seqlen_k) r[i] = 0xff800000u;
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                m4[u] = fmaxf(fmaxf(m4[u], __uint_as_float(r[i + u])), __uint_as_float(r[i + 4 + u]));
+                        }
+                    }
+                }
+                float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+                xch[(gj & 1u) * 256 + half * 128 + row] = mx;
+                asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+                mx = fmaxf(mx, xch[(gj & 1u) * 256 + (half ^ 1) * 128 + row]);
+                pf_stamp(p, tr, 2, j);
+                float alpha = 1.0f;
+                bool grow = false;
+                if (j == 0) {
+                    m_ref = mx;
+                } else if ((mx - m_ref) * sl2 > 8.0f) {
+                    alpha = fast_exp2((m_ref - mx) * sl2);
+                    m_ref = mx;
+                    l *= alpha;
+                    grow = true;
+                }
+                if (j > 0 && __any_sync(0xffffffffu, grow)) {      // warp-uniform: tcgen05.ld/st are warp-collective
+                    mbar_wait(bar(B3_PD + t), (gj - 1u) & 1u);     // P.V of tile j-1 retired: O stable
+                    tc_fence_after();
+#pragma unroll
+                    for (int c = 0; c < HD / 32; ++c) {
+                        uint32_t r[32];
+                        tmem_ld32(to + c * 32, r);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tmem_st32(to + c * 32, r);
+                    }
+                }
+                const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
+                float rs = 0.0f;
+                if (plain) {
+#pragma unroll
+                    for (int c = 0; c < HC / 32; ++c) {
+                        uint32_t r[32];
+                        uint32_t pw[16];
+                        tmem_ld32(ts + c * 32, r);
+                        tmem_wait_ld();
+                        rs += softmax_exp_tile<NPOLY, 32>(r, sl2, mr, pw);
+                        tmem_st16(ts + c * 16, pw);
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < HC / 32; ++c) {
+                        uint32_t r[32];
+                        uint32_t pw[16];
+                        const int c0 = n0 + c * 32;
+                        if ((c0 > qlo + 31) || (c0 >= seqlen_k)) {                    // dead chunk: P = 0
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) pw[i] = 0u;
+                            tmem_st16(ts + c * 16, pw);
+                            continue;
+                        }
+                        tmem_ld32(ts + c * 32, r);
+                        tmem_wait_ld();
+                        if ((c0 + 31 > qlo) || (c0 + 32 > seqlen_k)) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const int tok = n0 + c * 32 + i;
+                                if (tok > qpos || tok >= seqlen_k) r[i] = 0xff800000u;
+                            }
+                            rs += softmax_exp_tile<0, 32>(r, sl2, mr, pw);       // exact zeros for masked keys
+                        } else {
+                            rs += softmax_exp_tile<NPOLY, 32>(r, sl2, mr, pw);
+                        }
+                        tmem_st16(ts + c * 16, pw);
+                    }
+                }
+                l += rs;
+                pf_stamp(p, tr, 3, j);
+                pf_stamp(p, tr, 4, j);
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(bar(B3_PF + t));
+                pf_stamp(p, tr, 5, j);
+            }
+            g += (uint32_t)n_tiles;
+
+            // epilogue: row sum across the two halves, O / l -> bf16 -> global (each thread half of D).  The leading
+            // barrier also orders this item's write of lx behind the partner's read of the previous item's value.
+            asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+            lx[half * 128 + row] = l;
+            asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+            l += lx[(half ^ 1) * 128 + row];
+            if (p.trace != nullptr && tid == 64 && blockIdx.x == 0 && it < 64) p.trace[13 * 64 + it] = clock64();
+            mbar_wait(bar(B3_PD + t), (g - 1u) & 1u);
+            tc_fence_after();
+            if (p.trace != nullptr && tid == 64 && blockIdx.x == 0 && it < 64) p.trace[14 * 64 + it] = clock64();
+            const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
+            // TMEM hands every thread ITS OWN row (32 columns per tcgen05.ld): stored directly, one warp instruction
+            // touches 32 different 128-byte lines — 4096 line writes per item, ~2.3k clk of LSU time with the tensor
+            // pipe idle (profiles/r02/trace_prefill_s2048_persist.log: 3.6k clk from the last P.V to the end of the
+            // epilogue).  Transposed through a 1 KB per-warp staging tile ([16 rows][64 B], XOR-swizzled 16-byte units:
+            // conflict-free both ways) a warp instruction writes 8 rows x 64 contiguous bytes instead: 4x fewer lines.
+            uint8_t* stg = smem + C::OFF_STG + (warp - 2) * 1024;
+            __nv_bfloat16* obase = p.out + (int64_t)I.b * p.o_sb + (int64_t)hq * p.o_sh + half * HD;
+            const int row_w0 = q0 + quarter * 32;                        // first row of this warp
+#pragma unroll
+            for (int c = 0; c < HD / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld32(to + c * 32, r);
+                tmem_wait_ld();
+                uint4 v[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    v[i].x = pack_bf16(__uint_as_float(r[i * 8 + 0]) * inv, __uint_as_float(r[i * 8 + 1]) * inv);
+                    v[i].y = pack_bf16(__uint_as_float(r[i * 8 + 2]) * inv, __uint_as_float(r[i * 8 + 3]) * inv);
+                    v[i].z = pack_bf16(__uint_as_float(r[i * 8 + 4]) * inv, __uint_as_float(r[i * 8 + 5]) * inv);
+                    v[i].w = pack_bf16(__uint_as_float(r[i * 8 + 6]) * inv, __uint_as_float(r[i * 8 + 7]) * inv);
+                }
+#pragma unroll
+                for (int hr = 0; hr < 2; ++hr) {
+                    if ((lane >> 4) == hr) {
+                        const int rr = lane & 15;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            *reinterpret_cast<uint4*>(stg + rr * 64 + ((i ^ ((rr >> 1) & 3)) << 4)) = v[i];
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int k2 = 0; k2 < 2; ++k2) {
+                        const int u = lane + 32 * k2, rr = u >> 2, seg = u & 3;
+                        const uint4 w4 = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((seg ^ ((rr >> 1) & 3)) << 4));
+                        const int grow = row_w0 + hr * 16 + rr;
+                        if (grow < p.S)
+                            *reinterpret_cast<uint4*>(obase + (int64_t)grow * p.o_ss + c * 32 + seg * 8) = w4;
+                    }
+                    __syncwarp();
+                }
+            }
+            // the next item's first P.V overwrites O: it needs this thread's PF arrive, which comes after these loads
+            tc_fence_before();
+            if (p.trace != nullptr && tid == 64 && blockIdx.x == 0 && it < 64) p.trace[12 * 64 + it] = clock64();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1231,6 +1715,36 @@ static int launch_prefill_pair(const CUtensorMap& tq, const CUtensorMap& tk, con
     return 0;
 }
 
+template <class C, int SM>
+static int launch_prefill_persist(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                                  const PrefillParams& p, int* counter, int n_sm, cudaStream_t st) {
+    static int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_persist_kernel<C, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
+        attr_dev = dev;
+    }
+    PersistParams pp;
+    pp.p = p;
+    pp.pair_heads = (p.G % 2 == 0) ? 1 : 0;
+    const int q_tiles = (p.S + C::BM - 1) / C::BM;
+    pp.p.nx = pp.pair_heads ? q_tiles : (q_tiles + 1) / 2;
+    pp.p.ny = pp.pair_heads ? p.Hq / 2 : p.Hq;
+    const long long total = (long long)pp.p.nx * pp.p.ny * p.B;
+    if (total > 0x3fffffffLL) { set_error("prefill: too many work items"); return B200_E_RANGE; }
+    pp.total = (int)total;
+    pp.counter = counter;
+    const unsigned grid = (unsigned)(total < n_sm ? total : n_sm);     // one resident CTA per SM
+    static const bool pdl = []() { const char* e = getenv("B200_PREFILL_PDL"); return !(e && e[0] == '0'); }();
+    cudaError_t le = launch_maybe_pdl(prefill_attn_persist_kernel<C, SM>, dim3(grid), dim3(C::THREADS), (size_t)C::SMEM, st,
+                                      pdl, tq, tk, tv, pp);
+    if (le != cudaSuccess) { set_error("prefill launch failed: %s", cudaGetErrorString(le)); return (int)le; }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -1242,7 +1756,7 @@ extern "C" void b200_debug_prefill_trace(void* dev_buf) { g_prefill_trace = (lon
 
 extern "C" int64_t b200_prefill_workspace_bytes(int32_t B, int32_t S, int32_t Hq, int32_t D) {
     if (B <= 0 || S <= 0 || Hq <= 0 || D <= 0) return -1;
-    return (int64_t)B * S * Hq * D * 2;          // rotated Q, bf16
+    return (int64_t)B * S * Hq * D * 2 + 256;    // rotated Q (bf16) + the persistent kernel's work-item counter
 }
 
 extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream) {
@@ -1288,6 +1802,8 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     ap.kc_sblk = a->kc_stride_blk; ap.kc_stok = a->kc_stride_tok; ap.kc_sh = a->kc_stride_h;
     ap.vc_sblk = a->vc_stride_blk; ap.vc_stok = a->vc_stride_tok; ap.vc_sh = a->vc_stride_h;
     ap.bt_sb = a->bt_stride_b;
+    int* work_counter = reinterpret_cast<int*>((uint8_t*)a->workspace + (need - 256));
+    ap.work_counter = work_counter;
     prefill_rope_append_kernel<<<dim3((unsigned)a->S, (unsigned)a->B), 128, 0, st>>>(ap);
     B200_CHECK_LAUNCH();
 
@@ -1310,15 +1826,21 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
         return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
     }
     int variant = a->variant;
+    static int n_sm = 0;
+    if (n_sm == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
     if (variant == 0) {
-        // default: two Q tiles per CTA (half the K/V traffic, half the prologues per unit of work, ping-pong)
-        // whenever that grid still fills the GPU; the one-tile kernel for small grids
-        // (measured, profiles/r01/prefill_bench.json)
-        static int n_sm = 0;
-        if (n_sm == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+        // default: two Q tiles per work item (half the K/V traffic, ping-pong) on the persistent one-CTA-per-SM kernel
+        // whenever those items still fill the GPU; the one-tile kernel for small grids
         const long long q_tiles = (a->S + 127) / 128;
         const long long pair_ctas = ((p.G % 2 == 0) ? q_tiles * (a->Hq / 2) : ((q_tiles + 1) / 2) * a->Hq) * a->B;
-        if (pair_ctas >= n_sm) variant = 6;
+        if (pair_ctas >= n_sm) variant = 9;
+    }
+    if (variant >= 9 && variant <= 11) {  // persistent pair kernel; 9 / 10 / 11 = 25 % / 0 % / 50 % polynomial exp2
+#define B200_PS_DISPATCH(V, SMV) if (variant == V) { \
+        if (a->D == 128) return launch_prefill_persist<PCfg4<128>, SMV>(tq, tk, tv, p, work_counter, n_sm, st); \
+        return launch_prefill_persist<PCfg4<64>, SMV>(tq, tk, tv, p, work_counter, n_sm, st); }
+        B200_PS_DISPATCH(9, 2) B200_PS_DISPATCH(10, 1) B200_PS_DISPATCH(11, 3)
+#undef B200_PS_DISPATCH
     }
     if (variant >= 6 && variant <= 8) {   // two Q tiles per CTA (ping-pong); 6 / 7 / 8 = 25 % / 0 % / 50 % polynomial exp2
 #define B200_PP_DISPATCH(V, SMV) if (variant == V) { \

@@ -1,6 +1,5 @@
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_prefill.py -x -q > gpurun_out/pytest_prefill.log 2>&1; echo "pytest prefill rc=$?"; tail -3 gpurun_out/pytest_prefill.log
-timeout 1500 python -m pytest tests -m gpu -q --deselect tests/test_gpu_prefill.py > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rest rc=$?"; tail -5 gpurun_out/pytest_gpu.log
 timeout 600 python tools/bench_prefill.py > gpurun_out/bench_prefill.log 2>&1; echo "bench_prefill rc=$?"; grep -v "^$" gpurun_out/bench_prefill.log | cut -c1-420
 timeout 200 python tools/trace_prefill.py 0 2048 > gpurun_out/trace_prefill_s2048.log 2>&1; echo "trace rc=$?"; head -1 gpurun_out/trace_prefill_s2048.log
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:prefill --csv --log-file gpurun_out/launches_prefill_small.csv python tools/profile_prefill_small.py > gpurun_out/ncu_prefill_small.log 2>&1; echo "ncu prefill rc=$?"

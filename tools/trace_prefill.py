@@ -39,7 +39,7 @@ b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, vari
 torch.cuda.synchronize()
 _lib.lib.b200_debug_prefill_trace(None)
 t = buf.cpu().view(16, 64)
-nt = min(64, -(-S // 128))
+nt = min(64, -(-S // 128), int((t[11] != 0).sum()))    # CTA 0's first work item may not be the heaviest one
 t0 = int(t[9, 0])
 names = {0: "sm_S_ready", 1: "sm_S_loaded", 2: "sm_max_done", 3: "sm_exp_done", 4: "sm_PE_passed", 5: "sm_P_published",
          6: "mma_QK_issue", 7: "mma_PV_enter", 8: "mma_PV_issue", 9: "tma_K_issue", 10: "tma_V_issue", 11: "sm_tile_top"}
@@ -66,7 +66,9 @@ summ = {
 }
 item_ends = [int(x) - t0 for x in t[12].tolist() if int(x) != 0]
 print(json.dumps({"variant": variant, "S": S, "tiles": nt, "steady_state_clk": summ,
-                  "cta0_item_epilogue_done_clk": item_ends}))
+                  "cta0_item_epilogue_done_clk": item_ends,
+                  "cta0_item_epilogue_enter_clk": [int(x) - t0 for x in t[13].tolist() if int(x) != 0],
+                  "cta0_item_last_PV_retired_clk": [int(x) - t0 for x in t[14].tolist() if int(x) != 0]}))
 for j in list(range(0, min(6, nt))) + list(range(max(6, nt - 3), nt)):
     print(j, {kk: vv[j] for kk, vv in rel.items()})
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
