@@ -196,7 +196,7 @@ def _tune(name: str) -> int:
     return v
 
 
-def decode_use_balanced(batch: int, kv_heads: int, n_sm: int = 148) -> bool:
+def decode_use_balanced(batch: int, kv_heads: int, n_sm: int = 148, q_per_kv: int = 1) -> bool:
     """Whether the persistent stream-K form is the default for this launch shape (launch-time
     constants only).  ``B200_DECODE_BALANCED`` = 0 / 1 forces it off / on (tuning)."""
     global _BALANCED_ENV
@@ -207,7 +207,17 @@ def decode_use_balanced(batch: int, kv_heads: int, n_sm: int = 148) -> bool:
         return False
     if _BALANCED_ENV in ("0", "1"):
         return _BALANCED_ENV == "1"
-    return False
+    # Measured on B200 (profiles/r02/bench_ragged.jsonl): a split-KV grid that needs more than one wave of the
+    # 3 x #SMs resident CTAs and leaves its last wave mostly empty loses to the persistent form (Llama-3-70B heads,
+    # B = 64, 8k: 512 CTAs on 444 slots, 411 us vs 343 us = 0.80 -> 0.95 of the HBM peak); a grid that fits one wave
+    # does not (Qwen2.5-7B heads, B = 64, 2k: 256 CTAs, 45.5 us vs 59 us).
+    groups = max(1, -(-max(1, q_per_kv) // 16))
+    ctas = batch * kv_heads * groups
+    slots = 3 * n_sm
+    if ctas <= slots:
+        return False
+    waves = ctas / slots
+    return waves / math.ceil(waves) < 0.85
 
 
 _RETIRED: list = []
@@ -316,7 +326,7 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     a.vc_stride_blk, a.vc_stride_tok, a.vc_stride_h = v_cache.stride(0), v_cache.stride(1), v_cache.stride(2)
     a.bt_stride_b = block_table.stride(0)
     if balanced is None:
-        balanced = num_splits <= 0 and not pdl and decode_use_balanced(B, Hkv, sm_count(q.device))
+        balanced = num_splits <= 0 and not pdl and decode_use_balanced(B, Hkv, sm_count(q.device), Hq // Hkv)
     if num_splits <= 0:
         num_splits = 1 if balanced else decode_num_splits(B, Hkv, block_table.shape[1] * block_size,
                                                           sm_count(q.device))

@@ -270,7 +270,7 @@ class ModelGraphRunner:
                                   self.attention._cos_pool, self.attention._sin_pool,
                                   cache_lens, block_table, softmax_scale=self.attention.scale,
                                   rotary_interleaved=False, out=attn, pdl=0 if balanced else self.use_pdl,
-                                  balanced=balanced)
+                                  balanced=True if balanced else None)    # None: shape heuristic (tail waves)
         w_nk = getattr(block.attn, "_o_nk", None)
         if self._use_stream(bs, w_nk):
             return b200ops.stream_gemm(self._attn[:bs], w_nk, out=self._attn_out[:bs], pdl=self._stream_pdl)

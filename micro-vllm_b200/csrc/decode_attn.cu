@@ -20,6 +20,7 @@
 //   merge, so no second kernel launch is needed and the counter is left at 0
 //   (CUDA-graph replay safe).
 #include "common.cuh"
+#include <cstdlib>
 #include <math_constants.h>
 
 namespace b200 {
@@ -61,6 +62,7 @@ struct DecodeParams {
     int pdl;                             // launched with programmatic stream serialization
     unsigned long long* trace;           // debug only (b200_debug_decode_trace): [CTA][8] %globaltimer stamps
     int cluster;                         // the splits of a segment form one thread-block cluster: merge through DSMEM
+    int sk_ov;                           // balanced form: fixed cost of a segment, in chunks (see paged_decode_sk_kernel)
     int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, o_sb, o_sh;
     int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, bt_sb;
     float scale, scale_log2;
@@ -580,9 +582,15 @@ paged_decode_sk_kernel(const __grid_constant__ DecodeParams p) {
     const int B = p.B;
     const int add_new = p.k_new != nullptr ? 1 : 0;
 
+    // Shares are cut in WEIGHT units, not chunks: a (sequence, kv head, group) segment of n chunks weighs n + OV, the
+    // first OV units standing for the fixed cost of starting a piece (q load + RoPE, ring fill, warp merge, output:
+    // ~3 us = 1-2 chunks of streaming at a CTA's fair share of HBM).  With plain chunk counts the CTA that drew a run of
+    // 128-token sequences walked a dozen two-chunk pieces back to back and set the makespan of the launch (configs[2]:
+    // 89 us against 55 us of streaming, profiles/r02/bench_n1.log).
+    const int OV = p.sk_ov;
     for (int i = tid; i < B; i += C::THREADS) {
         const int len = __ldg(p.seqlens + i) + add_new;
-        s_pre[i + 1] = max(1, (len + C::CH - 1) / C::CH);         // an empty sequence still owns one (masked) chunk
+        s_pre[i + 1] = max(1, (len + C::CH - 1) / C::CH) + OV;    // an empty sequence still owns one (masked) chunk
     }
     if (tid == 0) s_pre[0] = 0;
     __syncthreads();
@@ -606,7 +614,7 @@ paged_decode_sk_kernel(const __grid_constant__ DecodeParams p) {
     const int Y = p.Hkv * p.ngroups;
     const int Wt = Y * s_pre[B];
     const int P = gridDim.x;
-    const int q = max(kSkMinChunks, (Wt + P - 1) / P);
+    const int q = max(kSkMinChunks + OV, (Wt + P - 1) / P);
     int gpos = blockIdx.x * q;
     const int gend = min(Wt, gpos + q);
 
@@ -617,12 +625,15 @@ paged_decode_sk_kernel(const __grid_constant__ DecodeParams p) {
             if (Y * s_pre[mid] <= gpos) lo = mid; else hi = mid - 1;
         }
         const int b = lo;
-        const int n_b = s_pre[b + 1] - s_pre[b];
+        const int w_b = s_pre[b + 1] - s_pre[b];                   // weight of one segment of this sequence
+        const int n_b = w_b - OV;                                  // its chunks
         const int rem = gpos - Y * s_pre[b];
-        const int y = rem / n_b;
-        const int cs = rem - y * n_b;
-        const int ce = min(n_b, cs + (gend - gpos));
-        const int seg0 = gpos - cs;                                // global chunk coordinate of the segment start
+        const int y = rem / w_b;
+        const int ws = rem - y * w_b;                              // weight range [ws, we) of this segment is mine
+        const int we = min(w_b, ws + (gend - gpos));
+        const int cs = max(0, ws - OV), ce = max(0, we - OV);      // -> chunk range [cs, ce)
+        if (ce <= cs) { gpos += we - ws; continue; }               // only the overhead zone of this segment
+        const int seg0 = gpos - ws + OV;                           // global weight coordinate of the segment's chunk 0
         const int c_first = seg0 / q, c_last = (seg0 + n_b - 1) / q;
         const int npieces = c_last - c_first + 1;
         const bool whole = npieces == 1;
@@ -694,7 +705,7 @@ paged_decode_sk_kernel(const __grid_constant__ DecodeParams p) {
             }
         }
         __syncthreads();                                           // shared memory is reused by the next piece
-        gpos += ce - cs;
+        gpos += we - ws;
     }
 }
 
@@ -776,7 +787,12 @@ static int launch_decode_sk(const DecodeParams& p, cudaStream_t st) {
     }
     int ctas = n_sm * C::MINB;
     if (ctas > kSkMaxCtas) ctas = kSkMaxCtas;
-    paged_decode_sk_kernel<C><<<ctas, C::THREADS, smem_bytes, st>>>(p);
+    // fixed cost of a piece in chunks: ~192 tokens of streaming (measured sweep, profiles/r02/bench_ragged.jsonl:
+    // configs[2] 93 us at 0, 77 us at 3 chunks of 64 tokens; B200_DECODE_SK_OV overrides, 0 = plain chunk balancing)
+    static const int ov_env = []() { const char* e = getenv("B200_DECODE_SK_OV"); return e ? atoi(e) : -1; }();
+    DecodeParams pk = p;
+    pk.sk_ov = ov_env >= 0 ? (ov_env > 64 ? 64 : ov_env) : (192 / C::CH > 1 ? 192 / C::CH : 1);
+    paged_decode_sk_kernel<C><<<ctas, C::THREADS, smem_bytes, st>>>(pk);
     B200_CHECK_LAUNCH();
     return 0;
 }

@@ -1,6 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_prefill.py -x -q > gpurun_out/pytest_prefill.log 2>&1; echo "pytest prefill rc=$?"; tail -3 gpurun_out/pytest_prefill.log
-timeout 600 python tools/bench_prefill.py > gpurun_out/bench_prefill.log 2>&1; echo "bench_prefill rc=$?"; grep -v "^$" gpurun_out/bench_prefill.log | cut -c1-420
-timeout 200 python tools/trace_prefill.py 0 2048 > gpurun_out/trace_prefill_s2048.log 2>&1; echo "trace rc=$?"; head -1 gpurun_out/trace_prefill_s2048.log
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:prefill --csv --log-file gpurun_out/launches_prefill_small.csv python tools/profile_prefill_small.py > gpurun_out/ncu_prefill_small.log 2>&1; echo "ncu prefill rc=$?"
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:prefill_attn -s 1 -c 1 -o gpurun_out/prefill_s2048_persist_r02 -f python tools/profile_prefill_small.py > gpurun_out/ncu_prefill.log 2>&1; echo "ncu prefill full rc=$?"
+for c in 1 2 4 8 16; do timeout 300 python bench.py --no-decode-step --no-configs --no-cpu-baseline --e2e-chunks $c 2>&1 | grep '^{' | python -c "import sys,json; j=json.loads(sys.stdin.read()); print('chunks', $c, 'value', j['value'], 'e2e', j['e2e']['value'], round(j['e2e']['value']/j['value'],4))"; done
+B200_DECODE_SK_OV=3 timeout 300 python tools/bench_ragged.py 2>&1 | grep '^{' | cut -c1-900
+timeout 900 python -m pytest tests/test_gpu_decode.py tests/test_gpu_model.py -x -q > gpurun_out/pytest_decode.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_decode.log
