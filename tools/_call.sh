@@ -1,4 +1,7 @@
 mkdir -p gpurun_out
-for c in 1 2 4 8 16; do timeout 300 python bench.py --no-decode-step --no-configs --no-cpu-baseline --e2e-chunks $c 2>&1 | grep '^{' | python -c "import sys,json; j=json.loads(sys.stdin.read()); print('chunks', $c, 'value', j['value'], 'e2e', j['e2e']['value'], round(j['e2e']['value']/j['value'],4))"; done
-B200_DECODE_SK_OV=3 timeout 300 python tools/bench_ragged.py 2>&1 | grep '^{' | cut -c1-900
-timeout 900 python -m pytest tests/test_gpu_decode.py tests/test_gpu_model.py -x -q > gpurun_out/pytest_decode.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_decode.log
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
+timeout 400 $TR --master-port 29541 bench.py --gpus 8 --steps 20 --warmup 3 > gpurun_out/bench_n8.log 2>&1; echo "bench n8 rc=$?"; grep '^{' gpurun_out/bench_n8.log | cut -c1-3300
+timeout 200 $TR --master-port 29542 tools/bench_decode_step.py --profile > gpurun_out/step_l70_tp8_profile.log 2>&1; echo "profile rc=$?"; grep -E '^\{|us/layer' gpurun_out/step_l70_tp8_profile.log | cut -c1-700
+B200_AR_MODE=nvlsp timeout 150 $TR --master-port 29543 tools/bench_decode_step.py > gpurun_out/step_l70_tp8_nvlsp.log 2>&1; echo "nvlsp rc=$?"; grep '^{' gpurun_out/step_l70_tp8_nvlsp.log | cut -c1-400
+B200_AR_MODE=nvls1 timeout 150 $TR --master-port 29544 tools/bench_decode_step.py > gpurun_out/step_l70_tp8_nvls1.log 2>&1; echo "nvls1 rc=$?"; grep '^{' gpurun_out/step_l70_tp8_nvls1.log | cut -c1-400
+timeout 150 $TR --master-port 29545 tools/bench_allreduce.py 64 > gpurun_out/allreduce_tp8.log 2>&1; echo "ar rc=$?"; grep '^{' gpurun_out/allreduce_tp8.log | python -c "import sys,json; j=json.loads(sys.stdin.read()); print({k:v for k,v in j.items() if k.endswith('_us')})"
