@@ -1437,6 +1437,7 @@ prefill_attn_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __gr
                 mbar_wait(bar(B3_SF + t), gj & 1u);
                 pf_stamp(p, tr, 0, j);
                 pf_stamp(p, tr, 1, j);
+                if (p.trace != nullptr && j == 0 && tid == 64 && blockIdx.x == 0 && it < 64) p.trace[15 * 64 + it] = clock64();
                 tc_fence_after();
                 // warp-uniform: a tile with no chunk reaching beyond qlo / seqlen_k takes the straight-line code
                 const bool plain = !((n0 + HC - 1 > qlo) || (n0 + HC > seqlen_k));

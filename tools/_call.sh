@@ -1,7 +1,7 @@
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
-timeout 400 $TR --master-port 29541 bench.py --gpus 8 --steps 20 --warmup 3 > gpurun_out/bench_n8.log 2>&1; echo "bench n8 rc=$?"; grep '^{' gpurun_out/bench_n8.log | cut -c1-3300
-timeout 200 $TR --master-port 29542 tools/bench_decode_step.py --profile > gpurun_out/step_l70_tp8_profile.log 2>&1; echo "profile rc=$?"; grep -E '^\{|us/layer' gpurun_out/step_l70_tp8_profile.log | cut -c1-700
-B200_AR_MODE=nvlsp timeout 150 $TR --master-port 29543 tools/bench_decode_step.py > gpurun_out/step_l70_tp8_nvlsp.log 2>&1; echo "nvlsp rc=$?"; grep '^{' gpurun_out/step_l70_tp8_nvlsp.log | cut -c1-400
-B200_AR_MODE=nvls1 timeout 150 $TR --master-port 29544 tools/bench_decode_step.py > gpurun_out/step_l70_tp8_nvls1.log 2>&1; echo "nvls1 rc=$?"; grep '^{' gpurun_out/step_l70_tp8_nvls1.log | cut -c1-400
-timeout 150 $TR --master-port 29545 tools/bench_allreduce.py 64 > gpurun_out/allreduce_tp8.log 2>&1; echo "ar rc=$?"; grep '^{' gpurun_out/allreduce_tp8.log | python -c "import sys,json; j=json.loads(sys.stdin.read()); print({k:v for k,v in j.items() if k.endswith('_us')})"
+timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/smoke.log
+timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1; echo "ref rc=$?"; tail -1 gpurun_out/bench_ref.log | cut -c1-200
+timeout 600 python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/bench.log | cut -c1-400
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/launches_bench.csv python bench.py --steps 2 --warmup 3 --no-decode-step --no-configs --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1; echo "ncu launches rc=$?"
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:paged_decode -s 3 -c 1 -o gpurun_out/decode_r02 -f python tools/profile_decode.py 6 0 0 > gpurun_out/ncu_decode.log 2>&1; echo "ncu decode rc=$?"

@@ -14,10 +14,11 @@ from core.paged_attention import build_rotary_tables  # noqa: E402
 
 variant = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 S = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
+B_arg = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 dev = torch.device("cuda")
 torch.manual_seed(0)
 bf = torch.bfloat16
-B, P, Hq, Hkv, D, page = 1, 0, 32, 8, 128, 256
+B, P, Hq, Hkv, D, page = B_arg, 0, 32, 8, 128, 256
 per_seq = -(-(P + S) // page)
 n_blocks = B * per_seq + 2
 kc = torch.randn(n_blocks, page, Hkv, D, device=dev, dtype=bf)
@@ -68,7 +69,8 @@ item_ends = [int(x) - t0 for x in t[12].tolist() if int(x) != 0]
 print(json.dumps({"variant": variant, "S": S, "tiles": nt, "steady_state_clk": summ,
                   "cta0_item_epilogue_done_clk": item_ends,
                   "cta0_item_epilogue_enter_clk": [int(x) - t0 for x in t[13].tolist() if int(x) != 0],
-                  "cta0_item_last_PV_retired_clk": [int(x) - t0 for x in t[14].tolist() if int(x) != 0]}))
+                  "cta0_item_last_PV_retired_clk": [int(x) - t0 for x in t[14].tolist() if int(x) != 0],
+                  "cta0_item_first_S_ready_clk": [int(x) - t0 for x in t[15].tolist() if int(x) != 0]}))
 for j in list(range(0, min(6, nt))) + list(range(max(6, nt - 3), nt)):
     print(j, {kk: vv[j] for kk, vv in rel.items()})
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
