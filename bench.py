@@ -29,8 +29,9 @@ own KV cache (16 GiB of KV per step >> 126 MB L2, nothing is served from cache b
             (core/layer/model_graph.py:210, :219) — outside the headline's timed region.
   tp_check (N > 1): fused NVLink reduction vs NCCL all_reduce on the same weights: ranks
             bit-identical, relative rms difference, no flag-wait timeout.
-  configs (N = 1): BASELINE.json configs[2] (64 ragged sequences) and configs[4] (batch 8, 128k
-            context) decode attention, prefill attention TFLOP/s, elementwise GB/s.
+  configs (N = 1): BASELINE.json configs[2] (64 ragged sequences: the 56 decode rows alone and the whole mixed
+            prefill + decode step) and configs[4] (batch 8, 128k context) decode attention, prefill attention
+            TFLOP/s, elementwise GB/s.  (N > 1): the per-GPU shard of configs[4] at TP = N.
   --impl reference : the reference semantics on the host CPU cores (oracle port, torch eager,
             all threads) on a bounded sample of the same workload.
 """
@@ -221,6 +222,46 @@ def _release():
     torch.cuda.empty_cache()
 
 
+# ---------------------------------------------------------------------------------- configs[4] shard (N > 1)
+def long_context_shard(dev, world, peak_gbs, emulate_rank_count=None):
+    """BASELINE.json configs[4] at TP = world: the per-GPU shard (Hq/world query heads, Hkv/world kv heads) of the batch-8,
+    128k-context decode attention call; every rank times its own shard (graph replay over two cache sets, CUDA events),
+    the figure is this rank's.  `whole_job_kv_GBps` = unsharded bytes / this rank's time."""
+    import b200ops
+    from core.paged_attention import build_rotary_tables
+    bf = torch.bfloat16
+    n = emulate_rank_count or world
+    Hq, Hkv, D, page, B, ctx = 32 // n, 8 // n, 128, 256, 8, 131072
+    per_seq = ctx // page
+    n_blocks = B * per_seq + 4
+    g = torch.Generator().manual_seed(0)
+    table = torch.randperm(n_blocks, generator=g)[: B * per_seq].view(B, per_seq).to(torch.int32).to(dev)
+    caches = [(torch.randn(n_blocks, page, Hkv, D, device=dev, dtype=bf),
+               torch.randn(n_blocks, page, Hkv, D, device=dev, dtype=bf)) for _ in range(2)]
+    cos, sin = build_rotary_tables(D, ctx + 8)
+    cos, sin = cos[:, : D // 2].contiguous().to(dev), sin[:, : D // 2].contiguous().to(dev)
+    lens = torch.full((B,), ctx - 1, dtype=torch.int32, device=dev)
+    q = torch.randn(B, Hq, D, device=dev, dtype=bf)
+    k = torch.randn(B, Hkv, D, device=dev, dtype=bf)
+    v = torch.randn(B, Hkv, D, device=dev, dtype=bf)
+    o = torch.empty(B, Hq, D, device=dev, dtype=bf)
+    calls = 4
+
+    def fn():
+        for i in range(calls):
+            kc, vc = caches[i % 2]
+            b200ops.paged_attn_decode(q, kc, vc, k, v, cos, sin, lens, table, out=o)
+    ms = _time_graph(_graph_of(fn)) / calls
+    local = b200ops.decode_algorithmic_bytes([ctx] * B, Hq, Hkv, D)
+    total = b200ops.decode_algorithmic_bytes([ctx] * B, 32, 8, D)
+    rec = {"tp": n, "Hq_local": Hq, "Hkv_local": Hkv, "us_per_call": round(ms * 1e3, 2),
+           "kv_GBps_per_gpu": round(local / ms / 1e6, 1), "frac_of_measured_hbm": round(local / ms / 1e6 / peak_gbs, 4),
+           "whole_job_kv_GBps": round(total / ms / 1e6, 1), "algorithmic_bytes_per_call_per_gpu": local}
+    del caches
+    _release()
+    return rec
+
+
 # ---------------------------------------------------------------------------------- secondary configs (N = 1)
 def secondary_configs(dev, peak_gbs, peak_tf):
     """BASELINE.json configs[2] / configs[4], prefill and elementwise figures; each timed on its own with
@@ -315,6 +356,22 @@ def secondary_configs(dev, peak_gbs, peak_tf):
     prefill_line("prefill_llama3-8b_b1_s2048", 1, 2048, 32, 8, 128)
     prefill_line("prefill_llama3-8b_b4_s512", 4, 512, 32, 8, 128)
     prefill_line("prefill_qwen2.5-0.5b_b4_s2048", 4, 2048, 14, 2, 64)
+
+    # configs[2] as ONE mixed step: 56 ragged decode rows (balanced launch) + 8 prefill chunks (512-2048 new tokens on
+    # cached prefixes) per layer, 4 of the 28 layers in one CUDA graph (tools/bench_continuous.py), flash-attn beside it
+    try:
+        from bench_continuous import run as run_mixed
+        mr = run_mixed(layers=4, with_flash_attn=True, verbose=False)
+        rec = dict(mr["b200"])
+        rec["layers_timed"] = 4
+        fa_ = mr.get("flash_attn_2.8.3", {})
+        rec["flash_attn_2.8.3_mixed_step_ms"] = fa_.get("mixed_step_ms")
+        rec["prefill_frac_of_sustained_bf16"] = round(rec["prefill_TFLOPs"] / peak_tf, 4)
+        rec["decode_frac_of_measured_hbm"] = round(rec["decode_kv_GBps_balanced"] / peak_gbs, 4)
+        out["cfg3_mixed_step_qwen2.5-7b_56_decode_rows_plus_8_prefill_chunks"] = rec
+    except Exception as e:  # noqa: BLE001
+        out["cfg3_mixed_step_qwen2.5-7b_56_decode_rows_plus_8_prefill_chunks"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    _release()
 
     # elementwise at 8192 rows (HBM-bound sizes), Llama-3-8B widths
     rows = 8192
@@ -544,6 +601,13 @@ def run_b200_arm(args):
         except Exception as e:  # noqa: BLE001
             tp_check = {"error": f"{type(e).__name__}: {e}"[:300]}
         _release()
+    long_ctx = None
+    if world > 1 and not args.no_configs:
+        try:
+            long_ctx = long_context_shard(dev, world, peak)
+        except Exception as e:  # noqa: BLE001
+            long_ctx = {"error": f"{type(e).__name__}: {e}"[:300]}
+        _release()
 
     if rank != 0:
         return
@@ -607,7 +671,7 @@ def run_b200_arm(args):
         "decode_step": step,
         "tp_check": tp_check,
         "decode_step_l8": step_l8,
-        "configs": configs,
+        "configs": configs if world == 1 else {"cfg5_llama3-8b_b8_128k_shard": long_ctx},
     }
     print(json.dumps(line), flush=True)
 

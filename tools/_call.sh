@@ -1,7 +1,3 @@
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
-timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/smoke.log
-timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1; echo "ref rc=$?"; tail -1 gpurun_out/bench_ref.log | cut -c1-200
-timeout 600 python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/bench.log | cut -c1-400
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/launches_bench.csv python bench.py --steps 2 --warmup 3 --no-decode-step --no-configs --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1; echo "ncu launches rc=$?"
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:paged_decode -s 3 -c 1 -o gpurun_out/decode_r02 -f python tools/profile_decode.py 6 0 0 > gpurun_out/ncu_decode.log 2>&1; echo "ncu decode rc=$?"
+timeout 300 python tools/_emul_long.py 2>&1 | tail -4
+timeout 600 python bench.py --no-decode-step --no-cpu-baseline > gpurun_out/bench_cfg.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/bench_cfg.log | python -c "import sys,json; j=json.loads(sys.stdin.read()); print(json.dumps(j['configs'],indent=0)[:3000])"

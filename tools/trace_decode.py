@@ -17,7 +17,7 @@ import b200ops  # noqa: E402
 from core.paged_attention import build_rotary_tables  # noqa: E402
 
 SHAPES = {"l8": dict(B=32, Hq=32, Hkv=8, D=128, ctx=4096), "l70tp8": dict(B=64, Hq=8, Hkv=1, D=128, ctx=8192),
-          "l70tp2": dict(B=64, Hq=32, Hkv=4, D=128, ctx=8192)}
+          "l70tp2": dict(B=64, Hq=32, Hkv=4, D=128, ctx=8192), "l8tp8": dict(B=32, Hq=4, Hkv=1, D=128, ctx=4096)}
 NAMES = ["entry", "loads_issued", "prologue_done", "first_stage", "loop_done", "partial_written", "exit", "merge_done"]
 
 

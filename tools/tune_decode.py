@@ -19,6 +19,8 @@ SHAPES = {
     "l8": dict(B=32, Hq=32, Hkv=8, D=128, ctx=4096),
     "l70tp8": dict(B=64, Hq=8, Hkv=1, D=128, ctx=8192),
     "l70tp2": dict(B=64, Hq=32, Hkv=4, D=128, ctx=8192),
+    "l8tp8": dict(B=32, Hq=4, Hkv=1, D=128, ctx=4096),        # per-GPU shard of bench.py --gpus 8
+    "l8tp4": dict(B=32, Hq=8, Hkv=2, D=128, ctx=4096),
     "q7": dict(B=64, Hq=28, Hkv=4, D=128, ctx=2048),
     "long": dict(B=8, Hq=32, Hkv=8, D=128, ctx=131072),
     "q05": dict(B=1, Hq=14, Hkv=2, D=64, ctx=192),
