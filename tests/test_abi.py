@@ -173,3 +173,18 @@ def test_sampler_and_new_ops_refuse_cpu_and_unsupported_modes():
     assert b200ops.skinny_gemm_ok(32, 14336, 4096) and b200ops.skinny_gemm_ok(1, 64, 64)
     assert not b200ops.skinny_gemm_ok(65, 4096, 4096) and not b200ops.skinny_gemm_ok(0, 64, 64)
     assert not b200ops.skinny_gemm_ok(8, 4096 + 32, 4096) and not b200ops.skinny_gemm_ok(8, 4096, 4096 + 8)
+
+
+def test_balanced_form_heuristic_is_a_launch_time_function_of_shape():
+    """b200ops.decode_use_balanced (pure host logic): the persistent stream-K form for split-KV grids that need more than
+    one wave of the 3 x #SMs resident CTAs and leave the last wave mostly empty (measured: profiles/r02/bench_ragged.jsonl),
+    the plain grid when everything fits one wave; never above the kernel's batch limit."""
+    import b200ops
+    f = b200ops.decode_use_balanced
+    assert f(64, 8, 148, 8) is True            # Llama-3-70B heads, B = 64: 512 CTAs on 444 slots
+    assert f(32, 8, 148, 4) is False           # config[1]: 256 CTAs, one wave
+    assert f(64, 4, 148, 7) is False           # Qwen2.5-7B heads, B = 64: 256 CTAs
+    assert f(111, 8, 148, 4) is False          # 888 CTAs = exactly two full waves
+    assert f(128, 8, 148, 4) is True           # 1024 CTAs: 2.3 waves
+    assert f(4096, 8, 148, 4) is False         # above DECODE_BALANCED_MAX_B
+    assert f(64, 1, 148, 40) is False          # 3 groups of 16 q heads: 192 CTAs
