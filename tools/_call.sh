@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-timeout 300 python tools/_emul_long.py 2>&1 | tail -4
-timeout 600 python bench.py --no-decode-step --no-cpu-baseline > gpurun_out/bench_cfg.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/bench_cfg.log | python -c "import sys,json; j=json.loads(sys.stdin.read()); print(json.dumps(j['configs'],indent=0)[:3000])"
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:greedy_argmax|paged_decode|prefill_|stream_gemm|topk_topp" -o gpurun_out/round2 -f python tools/profile_round2.py > gpurun_out/ncu_round2.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_round2.log; ls -la gpurun_out/round2.ncu-rep
