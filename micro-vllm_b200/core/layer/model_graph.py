@@ -84,7 +84,8 @@ class ModelGraphRunner:
         # B200_STREAM_GEMM: "auto" (default) sends a decode GEMM of <= 128 rows through the tcgen05 weight-streaming
         # kernel where it was measured faster than cuBLAS on B200 (profiles/r02/stream_gemm_*.json): deep-K, narrow-N
         # products (K >= 4 N: the QKV projection of a TP shard, where cuBLAS has too few tiles and no split-K and sits at
-        # 0.26 of the HBM roofline); "1" uses it for every shape it accepts, with the bias / SwiGLU epilogues fused;
+        # 0.26 of the HBM roofline; K >= 2 N at <= 32 rows: down_proj of the 8B shape); "1" uses it for every shape it
+        # accepts, with the bias / SwiGLU epilogues fused;
         # "0": cuBLAS + separate launches everywhere.  B200_STREAM_GEMM_PDL = 1 launches them with programmatic
         # dependent launch (weight boxes requested before the previous kernel has drained).
         self._stream_mode = os.environ.get("B200_STREAM_GEMM", "auto")
@@ -147,7 +148,7 @@ class ModelGraphRunner:
                 # (no copy); gate_up is interleaved row-wise (up_j, gate_j).
                 # (`.data`: plain tensors that keep the storage alive even if a caller later rebinds the Parameter)
                 def want(n, k):
-                    return self._stream_mode == "1" or k >= 4 * n
+                    return self._stream_mode == "1" or k >= 2 * n       # _use_stream decides per batch size
                 H = block.attn.c_attn.weight.shape[1]
                 if want((q_dim + 2 * kv_dim) // ws, H):
                     block.attn._qkv_nk = (block.attn.c_attn.weight.data if ws == 1 else
@@ -246,7 +247,11 @@ class ModelGraphRunner:
     def _use_stream(self, m, w_nk):
         if not (self._stream and w_nk is not None and b200ops.stream_gemm_ok(m, w_nk.shape[1], w_nk.shape[0])):
             return False
-        return self._stream_mode == "1" or w_nk.shape[1] >= 4 * w_nk.shape[0]
+        # measured (profiles/r02/stream_gemm_*.json): faster than cuBLAS for deep-K narrow-N products — K >= 4 N at any
+        # decode batch (QKV of a TP shard), K >= 2 N at <= 32 rows (Llama-3-8B down_proj: 24.6 us vs cuBLAS 28.6-32.5 us
+        # and 25.6 us for the round-1 mma.sync kernel, which this retires from the default path)
+        k, n = w_nk.shape[1], w_nk.shape[0]
+        return self._stream_mode == "1" or k >= 4 * n or (m <= 32 and k >= 2 * n)
 
     def _qkv_proj(self, block, bs):
         """QKV projection of ``self._normed[:bs]`` (the ln_1 norm was fused into the previous launch)."""
@@ -442,7 +447,7 @@ class ModelGraphRunner:
     def gemm_policy(self) -> str:
         """Which kernels run the four decode GEMMs (reported by the bench tools)."""
         if self._stream:
-            which = "every decode GEMM" if self._stream_mode == "1" else "K >= 4N products (QKV of a TP shard), cuBLAS elsewhere"
+            which = "every decode GEMM" if self._stream_mode == "1" else "K >= 4N products (QKV of a TP shard) and K >= 2N at <= 32 rows (down_proj), cuBLAS elsewhere"
             return (f"tcgen05 stream_gemm for {which}" +
                     (f" + PDL (L2 ahead {self._l2_ahead_kb} KB/CTA behind reductions)" if self._stream_pdl else "") +
                     (" + PDL reductions" if self._ar_pdl and self.world_size > 1 else ""))
