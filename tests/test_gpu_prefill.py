@@ -130,6 +130,39 @@ def test_prefill_persistent_few_items(B, S, Hq, Hkv, D, prefixes):
     check_prefill(make_paged_case(B, Hq, Hkv, D, prefixes, S_new=S, seed=S + Hq + 9), variant=9)
 
 
+@pytest.mark.parametrize("B,S,Hq,Hkv,D,prefix", [(1, 8192, 32, 8, 128, 0), (4, 2048, 14, 2, 64, 0), (2, 2048, 28, 4, 128, 6144)])
+def test_prefill_persistent_equals_one_cta_per_item_kernel_at_bench_sizes(B, S, Hq, Hkv, D, prefix):
+    """At the sizes the TFLOP/s figures are quoted on (64 KV tiles per item, > 1000 items, hundreds of ring wraps per
+    resident CTA) the fp32 CPU oracle is too slow to be the checker; the round-1 one-CTA-per-item kernel — itself checked
+    against the oracle on every smaller case — is.  With the MUFU-only softmax arithmetic (variants 10 and 7) both kernels
+    do the same operations in the same order per query tile, so the outputs must be BIT-IDENTICAL, whatever CTA ran an
+    item and however the items were interleaved; so must the K / V pages."""
+    page = 256
+    per_seq = -(-(prefix + S) // page)
+    n_blocks = B * per_seq + 3
+    g = torch.Generator(device="cuda").manual_seed(S + Hq)
+    dev = "cuda"
+    table = torch.randperm(n_blocks, device=dev)[: B * per_seq].view(B, per_seq).to(torch.int32)
+    lens = torch.full((B,), prefix, dtype=torch.int32, device=dev)
+    q, k, v = (torch.randn(B, S, h, D, device=dev, generator=g).to(torch.bfloat16) for h in (Hq, Hkv, Hkv))
+    from core.paged_attention import build_rotary_tables
+    cos, sin = build_rotary_tables(D, prefix + S + 1)
+    cos, sin = cos[:, : D // 2].contiguous().to(dev), sin[:, : D // 2].contiguous().to(dev)
+    outs, pages = [], []
+    for variant in (10, 7):
+        kc = torch.randn(n_blocks, page, Hkv, D, device=dev, generator=torch.Generator(device="cuda").manual_seed(5)).to(torch.bfloat16)
+        vc = torch.randn(n_blocks, page, Hkv, D, device=dev, generator=torch.Generator(device="cuda").manual_seed(6)).to(torch.bfloat16)
+        outs.append(b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, variant=variant))
+        pages.append((kc, vc))
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[0]).all()
+    assert torch.equal(outs[0], outs[1]), "persistent kernel and one-CTA-per-item kernel disagree"
+    assert torch.equal(pages[0][0], pages[1][0]) and torch.equal(pages[0][1], pages[1][1])
+    # and the default arithmetic (25 % polynomial exp2) stays within bf16 noise of it
+    dflt = b200ops.paged_attn_prefill(q, k, v, pages[0][0], pages[0][1], cos, sin, lens, table)
+    assert float((dflt.float() - outs[0].float()).abs().max()) < 2e-2
+
+
 def test_prefill_persistent_counter_rearmed_every_call():
     """The work-item counter lives in the call's workspace and is zeroed by the RoPE/append kernel of the SAME call:
     back-to-back calls and CUDA-graph replays must each see a fresh counter (a stale one would skip all work)."""
