@@ -180,287 +180,9 @@ __device__ __forceinline__ void pf_stamp(const PrefillParams& p, bool who, int e
         p.trace[ev * 64 + j] = clock64();
 }
 
-template <int D_>
-struct PCfg {
-    static constexpr int D = D_;
-    static constexpr int BM = 128, BN = 128;
-    static constexpr int SLAB_B = 128 * 128;                  // 128 rows x 128 B (64 bf16), one TMA box
-    static constexpr int DSLABS = D / 64;                     // slabs along head_dim
-    static constexpr int TILE_B = DSLABS * SLAB_B;            // Q, K or V tile
-    static constexpr int P_B = 2 * SLAB_B;                    // P [128 x 128 tokens] = 2 K-major slabs
-    static constexpr int KV_STAGES = 2;
-    static constexpr int OFF_Q = 0;
-    static constexpr int OFF_K = OFF_Q + TILE_B;
-    static constexpr int OFF_V = OFF_K + KV_STAGES * TILE_B;
-    static constexpr int OFF_P = OFF_V + KV_STAGES * TILE_B;
-    static constexpr int OFF_BAR = OFF_P + P_B;
-    static constexpr int NBARS = 16;
-    static constexpr int OFF_XCH = OFF_BAR + NBARS * 8 + 16;   // softmax row max / row sum exchange [2][2][128] f32
-    static constexpr int SMEM = OFF_XCH + 2 * 2 * 128 * 4 + 1024;   // +1024: manual 1 KB alignment
-    static constexpr int SOFTMAX_THREADS = 256;
-    static constexpr int THREADS = 64 + SOFTMAX_THREADS;      // warp0 TMA, warp1 MMA, warps 2-9 softmax
-    static constexpr int TMEM_COLS = 512;
-    static constexpr int TM_S0 = 0, TM_S1 = 128, TM_O = 256;
-};
-
-enum { BAR_Q = 0, BAR_KF = 1, BAR_KE = 3, BAR_VF = 5, BAR_VE = 7, BAR_SF = 9, BAR_SE = 11, BAR_PF = 13, BAR_PE = 14 };
-
-template <class C>
-__global__ void __launch_bounds__(C::THREADS, 1)
-prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                    const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ PrefillParams p) {
-    constexpr int D = C::D;
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t raw_u32 = smem_u32(smem_raw);
-    const uint32_t base = (raw_u32 + 1023u) & ~1023u;          // SWIZZLE_128B atoms need 1 KB alignment
-    uint8_t* smem = smem_raw + (base - raw_u32);
-    const uint32_t sQ = base + C::OFF_Q, sK = base + C::OFF_K, sV = base + C::OFF_V, sP = base + C::OFF_P;
-    const uint32_t bars = base + C::OFF_BAR;
-    auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
-    volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::NBARS * 8);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int qt = (int)gridDim.x - 1 - (int)blockIdx.x;       // heaviest (last) causal tiles first
-    const int q0 = qt * C::BM;
-    const int hq = blockIdx.y, b = blockIdx.z;
-    const int kvh = hq / p.G;
-    const int prefix = __ldg(p.seqlens + b);
-    const int seqlen_k = prefix + p.S;
-    const int kv_end = p.causal ? min(seqlen_k, prefix + q0 + C::BM) : seqlen_k;
-    const int n_tiles = (kv_end + C::BN - 1) / C::BN;
-
-    if (tid == 0) {
-        mbar_init(bar(BAR_Q), 1);
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(bar(BAR_KF + s), 1); mbar_init(bar(BAR_KE + s), 1);
-            mbar_init(bar(BAR_VF + s), 1); mbar_init(bar(BAR_VE + s), 1);
-            mbar_init(bar(BAR_SF + s), 1); mbar_init(bar(BAR_SE + s), C::SOFTMAX_THREADS);
-        }
-        mbar_init(bar(BAR_PF), C::SOFTMAX_THREADS); mbar_init(bar(BAR_PE), 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
-    }
-    if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                     :: "r"(smem_u32((const void*)s_tmem)), "r"((uint32_t)C::TMEM_COLS) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *s_tmem;
-
-    if (warp == 0) {
-        // ===================================================== TMA producer
-        if (lane == 0) {
-            mbar_expect_tx(bar(BAR_Q), C::TILE_B);
-#pragma unroll
-            for (int sl = 0; sl < C::DSLABS; ++sl)
-                tma_load_4d(sQ + sl * C::SLAB_B, &tm_q, bar(BAR_Q), sl * 64, hq, q0, b);
-            const int32_t* bt = p.block_table + (int64_t)b * p.bt_sb;
-            for (int j = 0; j < n_tiles; ++j) {
-                const int st = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-                const int n0 = j * C::BN;
-                const int pe = n0 / p.block_size;
-                int page = (pe < p.max_blocks_per_seq) ? __ldg(bt + pe) : 0;
-                if (page < 0 || page >= p.n_blocks) page = 0;          // memory safety; tokens are masked or undefined
-                const int tok = n0 - pe * p.block_size;
-                mbar_wait(bar(BAR_KE + st), ph ^ 1u);
-                mbar_expect_tx(bar(BAR_KF + st), C::TILE_B);
-#pragma unroll
-                for (int sl = 0; sl < C::DSLABS; ++sl)
-                    tma_load_4d(sK + st * C::TILE_B + sl * C::SLAB_B, &tm_k, bar(BAR_KF + st), sl * 64, kvh, tok, page);
-                mbar_wait(bar(BAR_VE + st), ph ^ 1u);
-                mbar_expect_tx(bar(BAR_VF + st), C::TILE_B);
-#pragma unroll
-                for (int sl = 0; sl < C::DSLABS; ++sl)
-                    tma_load_4d(sV + st * C::TILE_B + sl * C::SLAB_B, &tm_v, bar(BAR_VF + st), sl * 64, kvh, tok, page);
-            }
-        }
-    } else if (warp == 1) {
-        // ===================================================== MMA issuer (one thread)
-        if (lane == 0) {
-            constexpr uint32_t IDESC_QK = umma_idesc_bf16(C::BM, C::BN, 0, 0);   // A=Q K-major, B=K K-major
-            constexpr uint32_t IDESC_PV = umma_idesc_bf16(C::BM, D, 0, 1);       // A=P K-major, B=V MN-major
-            auto issue_pv = [&](int t) {
-                const int st = t & 1;
-                mbar_wait(bar(BAR_VF + st), (uint32_t)(t >> 1) & 1u);
-                if (t == n_tiles - 1 && seqlen_k - t * C::BN < C::BN)
-                    zero_v_tail<C::DSLABS>(sV + st * C::TILE_B, seqlen_k - t * C::BN, 0, 1);
-                mbar_wait(bar(BAR_PF), (uint32_t)t & 1u);
-                tc_fence_after();
-#pragma unroll
-                for (int k = 0; k < C::BN / 16; ++k) {
-                    // A: P[128 x 16 tokens], K-major slab k/4, +32 B per k-step inside the 128 B swizzle row
-                    const uint64_t da = umma_desc_sw128(sP + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
-                    // B: V[16 tokens x D], MN-major: 16 token rows = 2 KB per k-step, d-slabs 16 KB apart
-                    const uint64_t db = umma_desc_sw128(sV + st * C::TILE_B + k * 2048, C::SLAB_B, 1024);
-                    umma_bf16(tmem + C::TM_O, da, db, IDESC_PV, (t > 0 || k > 0) ? 1u : 0u);
-                }
-                tc_commit(bar(BAR_VE + st));       // V stage free once these MMAs retire
-                tc_commit(bar(BAR_PE));            // P buffer free, O updated
-            };
-            mbar_wait(bar(BAR_Q), 0);
-            for (int j = 0; j < n_tiles; ++j) {
-                const int st = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-                mbar_wait(bar(BAR_KF + st), ph);
-                mbar_wait(bar(BAR_SE + st), ph ^ 1u);
-                tc_fence_after();
-#pragma unroll
-                for (int k = 0; k < D / 16; ++k) {
-                    const uint64_t da = umma_desc_sw128(sQ + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
-                    const uint64_t db = umma_desc_sw128(sK + st * C::TILE_B + (k >> 2) * C::SLAB_B + (k & 3) * 32, 16, 1024);
-                    umma_bf16(tmem + (st ? C::TM_S1 : C::TM_S0), da, db, IDESC_QK, k > 0 ? 1u : 0u);
-                }
-                tc_commit(bar(BAR_KE + st));
-                tc_commit(bar(BAR_SF + st));
-                if (j > 0) issue_pv(j - 1);        // QK_j is queued ahead of PV_{j-1}: tensor pipe works while softmax j-1 runs
-            }
-            issue_pv(n_tiles - 1);
-        }
-    } else {
-        // ===================================================== softmax / correction / epilogue
-        // 8 warps: TWO threads per query row (TMEM lane = row; warps w and w+4 share a lane quarter),
-        // each owning 64 of the 128 key columns of a tile and half of the O columns.
-        const int quarter = warp & 3;                          // TMEM lane quarter this warp may access
-        const int half = (warp - 2) >> 2;                      // which 64 key columns / which half of D
-        const int row = quarter * 32 + lane;
-        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
-        const int qpos = p.causal ? (prefix + q0 + row) : 0x7fffffff;
-        const float sl2 = p.scale_log2;
-        constexpr int HC = C::BN / 2;                          // key columns per thread
-        constexpr int HD = D / 2;                              // O columns per thread
-        float m_ref = -CUDART_INF_F, l = 0.0f;
-        const uint32_t p_row = sP + (uint32_t)half * C::SLAB_B + (uint32_t)row * 128u;
-        const int sw = row & 7;
-        volatile float* xch = reinterpret_cast<volatile float*>(smem + C::OFF_XCH);   // [2 parity][2 halves][128 rows]
-
-        for (int j = 0; j < n_tiles; ++j) {
-            const int st = j & 1;
-            const int n0 = j * C::BN + half * HC;
-            mbar_wait(bar(BAR_SF + st), (uint32_t)(j >> 1) & 1u);
-            tc_fence_after();
-            uint32_t su[HC];                                   // scores, fp32 bit patterns (TMEM registers)
-#define SF(c) __uint_as_float(su[(c)])
-            {
-                const uint32_t ts = tmem + lane_sel + (st ? C::TM_S1 : C::TM_S0) + half * HC;
-#pragma unroll
-                for (int c = 0; c < HC / 32; ++c) {
-                    uint32_t r[32];
-                    tmem_ld32(ts + c * 32, r);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) su[c * 32 + i] = r[i];
-                }
-                tmem_wait_ld();
-            }
-            tc_fence_before();
-            mbar_arrive(bar(BAR_SE + st));                     // S buffer may be overwritten by QK_{j+2}
-
-            if (n0 + HC - 1 > prefix + q0 || n0 + HC > seqlen_k) {   // diagonal or tail columns
-#pragma unroll
-                for (int c = 0; c < HC; ++c) {
-                    const int tok = n0 + c;
-                    if (tok > qpos || tok >= seqlen_k) su[c] = 0xff800000u;   // -inf
-                }
-            }
-            float mx = SF(0);
-#pragma unroll
-            for (int c = 1; c < HC; ++c) mx = fmaxf(mx, SF(c));
-            // row max across the two column halves (parity-double-buffered exchange)
-            xch[(j & 1) * 256 + half * 128 + row] = mx;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            mx = fmaxf(mx, xch[(j & 1) * 256 + (half ^ 1) * 128 + row]);
-            // lazy rescale: keep the old reference max unless it is off by more than 2^8
-            // (both threads of a row take the same decision from the same numbers)
-            float alpha = 1.0f;
-            bool grow = false;
-            if (j == 0) {
-                m_ref = mx;
-            } else if ((mx - m_ref) * sl2 > 8.0f) {
-                alpha = fast_exp2((m_ref - mx) * sl2);
-                m_ref = mx;
-                l *= alpha;
-                grow = true;
-            }
-            const float mr = (m_ref == -CUDART_INF_F) ? 0.0f : m_ref * sl2;
-            float rs = 0.0f;
-#pragma unroll
-            for (int c = 0; c < HC; ++c) { const float e = fast_exp2(SF(c) * sl2 - mr); su[c] = __float_as_uint(e); rs += e; }
-            l += rs;
-
-            mbar_wait(bar(BAR_PE), ((uint32_t)j & 1u) ^ 1u);   // PV_{j-1} retired: P buffer free, O stable
-            tc_fence_after();
-#pragma unroll
-            for (int c = 0; c < HC / 8; ++c) {                 // 16-byte chunks of 8 tokens, K-major SW128 slab `half`
-                uint4 v;
-                v.x = pack_bf16(SF(c * 8 + 0), SF(c * 8 + 1));
-                v.y = pack_bf16(SF(c * 8 + 2), SF(c * 8 + 3));
-                v.z = pack_bf16(SF(c * 8 + 4), SF(c * 8 + 5));
-                v.w = pack_bf16(SF(c * 8 + 6), SF(c * 8 + 7));
-                const uint32_t addr = p_row + (uint32_t)((c ^ sw) << 4);
-                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-            }
-            if (j > 0 && __any_sync(0xffffffffu, grow)) {      // warp-uniform: tcgen05.ld/st are warp-collective
-                const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
-#pragma unroll
-                for (int c = 0; c < HD / 32; ++c) {
-                    uint32_t r[32];
-                    tmem_ld32(to + c * 32, r);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-                    tmem_st32(to + c * 32, r);
-                }
-                tmem_wait_st();
-            }
-            fence_async_smem();                                // P (generic proxy) -> visible to the tensor core (async proxy)
-            tc_fence_before();
-            mbar_arrive(bar(BAR_PF));
-#undef SF
-        }
-
-        // epilogue: row sum across the two halves, O / l -> bf16 -> global (each thread half of D)
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        xch[half * 128 + row] = l;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        l += xch[(half ^ 1) * 128 + row];
-        mbar_wait(bar(BAR_PE), (uint32_t)(n_tiles - 1) & 1u);
-        tc_fence_after();
-        const float inv = (l > 0.0f) ? 1.0f / l : 0.0f;
-        const bool live = (q0 + row) < p.S;
-        __nv_bfloat16* orow = p.out + (int64_t)b * p.o_sb + (int64_t)(q0 + row) * p.o_ss + (int64_t)hq * p.o_sh + half * HD;
-        const uint32_t to = tmem + lane_sel + C::TM_O + half * HD;
-#pragma unroll
-        for (int c = 0; c < HD / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld32(to + c * 32, r);
-            tmem_wait_ld();
-            if (live) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    uint4 v;
-                    v.x = pack_bf16(__uint_as_float(r[i * 8 + 0]) * inv, __uint_as_float(r[i * 8 + 1]) * inv);
-                    v.y = pack_bf16(__uint_as_float(r[i * 8 + 2]) * inv, __uint_as_float(r[i * 8 + 3]) * inv);
-                    v.z = pack_bf16(__uint_as_float(r[i * 8 + 4]) * inv, __uint_as_float(r[i * 8 + 5]) * inv);
-                    v.w = pack_bf16(__uint_as_float(r[i * 8 + 6]) * inv, __uint_as_float(r[i * 8 + 7]) * inv);
-                    *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
-                }
-            }
-        }
-    }
-
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)C::TMEM_COLS) : "memory");
-    }
-}
-
 // ------------------------------------------------------------------ kernel 2b: attention, operands in TMEM
-// Same pipeline as prefill_attn_kernel, but the two A operands never touch shared memory: the
+// First-round kernel (one query tile per CTA; its predecessor with Q and P staged in shared memory is in the
+// git history, retired in round 2).  The two A operands never touch shared memory: the
 // rotated Q tile is written ONCE into tensor memory (tcgen05.st by the softmax warps) and the
 // probabilities P go registers -> TMEM as packed bf16x2.  With Q and P in shared memory every KV
 // tile moves 224 KB through the 128 B/clk shared-memory port (MMA operand reads 128 KB, P 32 KB,
@@ -1654,23 +1376,6 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t d, uint64_t hea
     return 0;
 }
 
-template <class C>
-static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
-                          const PrefillParams& p, cudaStream_t st) {
-    static int attr_dev = -1;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (attr_dev != dev) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) { set_error("prefill: cannot opt in to %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e)); return (int)e; }
-        attr_dev = dev;
-    }
-    dim3 grid((unsigned)((p.S + C::BM - 1) / C::BM), (unsigned)p.Hq, (unsigned)p.B);
-    prefill_attn_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tq, tk, tv, p);
-    B200_CHECK_LAUNCH();
-    return 0;
-}
-
 template <class C, int SM>
 static int launch_prefill_tmem(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q_rot,
                                const PrefillParams& p, cudaStream_t st) {
@@ -1822,10 +1527,7 @@ extern "C" int b200_paged_attn_prefill(const b200_prefill_args* a, void* stream)
     p.scale_log2 = a->softmax_scale * 1.4426950408889634f;
     p.nx = p.ny = 0;
     p.trace = g_prefill_trace;
-    if (a->variant == 1) {                      // operands staged in shared memory (first version, kept for A/B runs)
-        if (a->D == 128) return launch_prefill<PCfg<128>>(tq, tk, tv, p, st);
-        return launch_prefill<PCfg<64>>(tq, tk, tv, p, st);
-    }
+    if (a->variant == 1) B200_FAIL(B200_E_RANGE, "prefill: variant 1 (operands staged in shared memory) was retired in round 2");
     int variant = a->variant;
     static int n_sm = 0;
     if (n_sm == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }

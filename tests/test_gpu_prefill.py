@@ -56,10 +56,14 @@ def test_prefill_long_prompt_many_tiles():
     check_prefill(case)
 
 
-@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
-def test_prefill_smem_operand_variant(D, Hq, Hkv):
-    """variant 1 = the first kernel (Q and P staged in shared memory), kept for A/B measurements."""
-    check_prefill(make_paged_case(2, Hq, Hkv, D, [0, 300], S_new=390, seed=31), variant=1)
+def test_prefill_retired_variant_is_refused():
+    """variant 1 (the first kernel: Q and P staged in shared memory) was retired in round 2: asking for it must fail
+    loudly, not fall through to another kernel."""
+    case = make_paged_case(1, 8, 2, 128, [0], S_new=64, seed=31)
+    d = to_dev(case)
+    with pytest.raises(b200ops.B200Error):
+        b200ops.paged_attn_prefill(d["q"], d["k"], d["v"], d["k_cache"], d["v_cache"], d["cos"], d["sin"], d["seqlens"],
+                                   d["table"], softmax_scale=case["scale"], variant=1)
 
 
 @pytest.mark.parametrize("variant", [2, 3, 4, 5])
@@ -243,7 +247,7 @@ def test_prefill_then_decode_consistency():
     assert_close(last, full[:, S].float(), what="decode vs last prefill row")
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 6, 9])
+@pytest.mark.parametrize("variant", [0, 2, 6, 9])
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 14, 2)])
 def test_prefill_poisoned_cache_tail(variant, D, Hq, Hkv):
     """never-written cache slots may hold NaN / Inf (torch.empty caches, recycled pages).  Keys at or

@@ -68,9 +68,8 @@ def main():
         with torch.cuda.graph(g):
             b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out)
         ms_graph = timeit(g.replay)
-        ms1 = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=1))
         rec = dict(case=name, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), graph_ms=round(ms_graph, 4),
-                   graph_tflops=round(flops / ms_graph / 1e9, 1), smem_variant_tflops=round(flops / ms1 / 1e9, 1))
+                   graph_tflops=round(flops / ms_graph / 1e9, 1))
         for var, key in ((4, "sm_poly25"), (6, "pair_poly25"), (9, "persist_poly25"), (10, "persist_packed"), (11, "persist_poly50")):
             msv = timeit(lambda: b200ops.paged_attn_prefill(q, k, v, kc, vc, cos, sin, lens, table, out=out, variant=var))
             rec[key + "_tflops"] = round(flops / msv / 1e9, 1)
