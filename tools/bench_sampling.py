@@ -1,4 +1,6 @@
-"""Greedy arg-max kernel vs torch.argmax on decode-sized logits (L2 flushed between launches).  GPU box only."""
+"""Token-selection kernels on decode-sized logits (L2 flushed between launches): greedy arg-max vs torch.argmax, and the
+top-k / top-p sampling kernel vs the reference sampler body (core/layer/sampler.py:21-43) restated in torch eager.
+GPU box only."""
 import json
 import os
 import sys
@@ -40,6 +42,59 @@ for rows, vocab in [(1, 152064), (32, 152064), (32, 128256), (64, 128256), (512,
     gbs = rows * vocab * 2 / t_our / 1e3
     rows_out.append(dict(rows=rows, vocab=vocab, b200_us=round(t_our, 2), torch_argmax_us=round(t_torch, 2),
                          GBps=round(gbs, 1), frac_of_measured_hbm=round(gbs / PEAK, 3)))
+    print(json.dumps(rows_out[-1]))
+
+
+def torch_sampler(logits, temps, top_ps, k):
+    """The reference's _sample_impl (sampler.py:21-43) in eager torch (the reference compiles it with Inductor)."""
+    x = logits.float() / temps[:, None]
+    vals, idxs = torch.topk(x, k, dim=-1)
+    probs = torch.softmax(vals, dim=-1)
+    sp, si = torch.sort(probs, dim=-1, descending=True)
+    cum = torch.cumsum(sp, dim=-1)
+    valid = cum < top_ps[:, None]
+    valid[:, 0] = True
+    sp = sp * valid
+    sp = sp / sp.sum(dim=-1, keepdim=True)
+    pick = torch.multinomial(sp, 1)
+    return idxs.gather(1, si.gather(1, pick)).squeeze(1)
+
+
+def graph_us(fn, copies, reps=5):
+    """Kernel time without the Python / ctypes launch path: `copies` calls over different logits tensors (together
+    larger than L2) captured in one CUDA graph, replayed `reps` times."""
+    for i in range(copies):
+        fn(i)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(copies):
+            fn(i)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (reps * copies)
+
+
+for rows, vocab, k in [(32, 152064, 50), (64, 128256, 50), (64, 128256, 1000), (1, 128256, 50)]:
+    copies = max(2, min(16, int(160e6 // (rows * vocab * 2)) + 1))
+    xs = [torch.randn(rows, vocab, device="cuda").to(torch.bfloat16) for _ in range(copies)]
+    x = xs[0]
+    temps = torch.full((rows,), 0.8, device="cuda")
+    tps = torch.full((rows,), 0.9, device="cuda")
+    un = torch.rand(rows, device="cuda")
+    out = torch.empty(rows, dtype=torch.int64, device="cuda")
+    t_graph = graph_us(lambda i: b200ops.topk_topp_sample(xs[i], temps, tps, k, un, out=out), copies)
+    t_our = timed(lambda: b200ops.topk_topp_sample(x, temps, tps, k, un, out=out))
+    t_torch = timed(lambda: torch_sampler(x, temps, tps, k))
+    rows_out.append(dict(op="topk_topp_sample", rows=rows, vocab=vocab, top_k=k, b200_graph_us=round(t_graph, 2),
+                         b200_eager_call_us=round(t_our, 2), torch_eager_reference_sampler_us=round(t_torch, 2)))
+    del xs
     print(json.dumps(rows_out[-1]))
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 json.dump(rows_out, open(os.path.join(ROOT, "gpurun_out", "sampling_bench.json"), "w"), indent=1)
