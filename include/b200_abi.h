@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 16
+#define B200_ABI_VERSION 17
 
 /* argument errors */
 #define B200_E_NULL        (-1)  /* required pointer is NULL            */
@@ -119,6 +119,37 @@ int b200_greedy_argmax(const void* logits, int logits_dtype,
                        int64_t* out_ids,
                        void* workspace, int64_t workspace_bytes,
                        void* stream);
+
+/* ------------------------------------------------------------------------ *
+ * Arg-max without a caller workspace.  NO COUNTERPART IN THE REFERENCE: this
+ * entry exists for hosts that cannot allocate device memory themselves, not to
+ * replace a reference call.
+ *
+ * Who needs it: an engine that sized its KV pool to fill the GPU and has
+ * nothing left for a late cudaMalloc; a latency-critical decode loop that must
+ * not pay cudaMalloc's device-wide synchronisation; a cgo / JNI / ctypes host
+ * that owns only the logits and the id buffer it passes in.  For them the
+ * scratch that b200_greedy_argmax asks the caller for (16 bytes per row) is a
+ * fixed array inside the library: B200_ARGMAX_NOALLOC_MAX_ROWS * 16 bytes =
+ * 64 KiB, resident on every GPU that loads libb200ops.so until the process
+ * exits.  Nothing is allocated or freed by this call, on any path.
+ *
+ * Same inputs, outputs and result as b200_greedy_argmax (FIRST index of the
+ * row maximum, int64), minus the workspace arguments.
+ *   rows > B200_ARGMAX_NOALLOC_MAX_ROWS -> B200_E_RANGE (use the workspace form).
+ *   The first call on each device looks up the array's device address (that
+ *     device must be current, as for every entry here); make that first call
+ *     before starting any stream capture on the device.
+ *   All calls on one device share the one array.  Each call clears the part it
+ *     uses in stream order, so back-to-back calls on ONE stream are fine; calls
+ *     that can run concurrently on the GPU (different streams, or different
+ *     host threads feeding different streams) race on it and must be serialised
+ *     by the caller.
+ * ------------------------------------------------------------------------ */
+#define B200_ARGMAX_NOALLOC_MAX_ROWS 4096
+int b200_greedy_argmax_noalloc(const void* logits, int logits_dtype,
+                               int64_t rows, int64_t vocab, int64_t stride,
+                               int64_t* out_ids, void* stream);
 
 /* Top-k / top-p sampling: replaces the reference's Inductor-compiled Sampler._sample_impl
  * (/root/reference/core/layer/sampler.py:21-43; called with top_k = 50 for decode, 1000 for prefill,

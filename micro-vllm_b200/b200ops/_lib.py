@@ -15,7 +15,7 @@ _i32, _i64, _f32, _vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 E_NULL, E_SHAPE, E_ALIGN, E_RANGE, E_UNSUPPORTED = -1, -2, -3, -4, -5
 DT_BF16, DT_F32 = 0, 1
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 
 class DecodeArgs(C.Structure):
@@ -118,6 +118,7 @@ SIGNATURES = {
                                       _i64, _i64, _i64, _i64, _i64, _vp]),
     "b200_greedy_argmax_workspace_bytes": (_i64, [_i64]),
     "b200_greedy_argmax": (C.c_int, [_vp, C.c_int, _i64, _i64, _i64, _vp, _vp, _i64, _vp]),
+    "b200_greedy_argmax_noalloc": (C.c_int, [_vp, C.c_int, _i64, _i64, _i64, _vp, _vp]),
     "b200_topk_topp_sample": (C.c_int, [_vp, C.c_int, _i64, _i64, _i64, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200_table_advance": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _i64, C.c_int, C.c_int, _vp, C.c_int, _vp]),
     "b200_l2_prefetch": (C.c_int, [_vp, _i64, _i64, _i64, _vp]),

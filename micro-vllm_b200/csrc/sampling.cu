@@ -374,6 +374,80 @@ extern "C" int b200_greedy_argmax(const void* logits, int logits_dtype, int64_t 
     return 0;
 }
 
+// ------------------------------------------------------------------ arg-max for callers that cannot allocate
+// Same kernel as b200_greedy_argmax, but the per-row merge scratch (one 64-bit key + one arrival counter per row)
+// lives in the library image instead of a caller buffer.  Meant for hosts that have no way to hand over device
+// scratch: a serving process whose KV pool already took every spare byte of HBM (a late cudaMalloc would fail),
+// a decode loop that cannot afford cudaMalloc's device-wide synchronisation, or a cgo / JNI binding that only
+// owns its input and output buffers.  Every GPU that loads libb200ops.so carries these 64 KiB until exit.
+static __device__ __align__(256) unsigned char g_argmax_static_scratch[B200_ARGMAX_NOALLOC_MAX_ROWS * 16];
+
+namespace {
+constexpr int kMaxDevices = 64;
+// Device address of g_argmax_static_scratch per device ordinal.  In host code the symbol name above is only a
+// handle for the runtime, not something a kernel can dereference, so the real address is looked up once per device
+// (with that device current) and cached here.  Racing first calls resolve the same value: the store is benign.
+void* g_argmax_static_ptr[kMaxDevices] = {};
+
+int argmax_static_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { ::b200::set_error("greedy_argmax_noalloc: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+    if (dev < 0 || dev >= kMaxDevices) B200_FAIL(B200_E_RANGE, "greedy_argmax_noalloc: device ordinal %d (0..%d)", dev, kMaxDevices - 1);
+    void* p = __atomic_load_n(&g_argmax_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress(&p, g_argmax_static_scratch);
+        if (e != cudaSuccess || !p) {
+            ::b200::set_error("greedy_argmax_noalloc: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+        }
+        __atomic_store_n(&g_argmax_static_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+}  // namespace
+
+extern "C" int b200_greedy_argmax_noalloc(const void* logits, int logits_dtype, int64_t rows, int64_t vocab,
+                                          int64_t stride, int64_t* out_ids, void* stream) {
+    if (!logits || !out_ids) B200_FAIL(B200_E_NULL, "greedy_argmax_noalloc: null pointer");
+    if (rows < 0 || vocab <= 0 || vocab > 0x7fffffffLL || stride < vocab)
+        B200_FAIL(B200_E_RANGE, "greedy_argmax_noalloc: rows=%lld vocab=%lld stride=%lld", (long long)rows,
+                  (long long)vocab, (long long)stride);
+    if (rows > B200_ARGMAX_NOALLOC_MAX_ROWS)
+        B200_FAIL(B200_E_RANGE, "greedy_argmax_noalloc: rows=%lld exceeds the built-in scratch (%d rows); use "
+                  "b200_greedy_argmax with a caller workspace", (long long)rows, B200_ARGMAX_NOALLOC_MAX_ROWS);
+    if (logits_dtype != B200_DT_BF16 && logits_dtype != B200_DT_F32)
+        B200_FAIL(B200_E_UNSUPPORTED, "greedy_argmax_noalloc: logits dtype %d", logits_dtype);
+    if (rows == 0) return 0;
+    void* scratch = nullptr;
+    if (int rc = argmax_static_scratch(&scratch)) return rc;     // first call per device: resolves the address
+    cudaStream_t st = (cudaStream_t)stream;
+    // The array is shared by every call and keeps whatever the previous one left (an aborted launch could leave
+    // keys or counters behind), so the part this call uses is zeroed in stream order before the kernel reads it.
+    cudaError_t e = cudaMemsetAsync(scratch, 0, (size_t)rows * 16, st);
+    if (e != cudaSuccess) { ::b200::set_error("greedy_argmax_noalloc: clearing scratch: %s", cudaGetErrorString(e)); return (int)e; }
+    const int n = logits_dtype == B200_DT_BF16 ? 8 : 4;
+    const int esz = logits_dtype == B200_DT_BF16 ? 2 : 4;
+    const int64_t per_cta = (int64_t)AM_CHUNK_VEC * n;
+    const int nchunks = (int)((vocab + per_cta - 1) / per_cta);
+    auto keys = (unsigned long long*)scratch;
+    auto arrivals = (unsigned int*)((char*)scratch + rows * 8);
+    const bool vec = aligned16(logits) && ((stride * esz) % 16 == 0) && vocab >= n;
+    const dim3 grid((unsigned)nchunks, (unsigned)rows);
+    if (logits_dtype == B200_DT_BF16) {
+        auto L = (const __nv_bfloat16*)logits;
+        if (vec) greedy_argmax_kernel<__nv_bfloat16, true><<<grid, AM_THREADS, 0, st>>>(L, stride, (int)vocab, nchunks, keys, arrivals, out_ids);
+        else     greedy_argmax_kernel<__nv_bfloat16, false><<<grid, AM_THREADS, 0, st>>>(L, stride, (int)vocab, nchunks, keys, arrivals, out_ids);
+    } else {
+        auto L = (const float*)logits;
+        if (vec) greedy_argmax_kernel<float, true><<<grid, AM_THREADS, 0, st>>>(L, stride, (int)vocab, nchunks, keys, arrivals, out_ids);
+        else     greedy_argmax_kernel<float, false><<<grid, AM_THREADS, 0, st>>>(L, stride, (int)vocab, nchunks, keys, arrivals, out_ids);
+    }
+    B200_CHECK_LAUNCH();
+    return 0;
+}
+
 extern "C" int b200_topk_topp_sample(const void* logits, int logits_dtype, int64_t rows, int64_t vocab, int64_t stride,
                                      int top_k, const float* temperatures, const float* top_ps, const float* uniforms,
                                      int64_t* out_ids, int32_t* dbg_idx, float* dbg_prob, void* stream) {
