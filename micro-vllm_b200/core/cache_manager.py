@@ -106,6 +106,7 @@ class KVCacheManager:
             up = torch.zeros(1 + 3 * self.max_table_updates, dtype=torch.int32, pin_memory=self._on_gpu)
             self._upd_stages.append({"t": up, "np": up.numpy(), "event": None})
         self._upd_idx = 0
+        self._updates_pending = False       # an uploaded update list no device launch has consumed yet
 
     # ------------------------------------------------------------------ allocator
     def alloc(self, seq_id: int, n_tokens: int) -> Tuple[bool, Optional[torch.Tensor]]:
@@ -192,6 +193,11 @@ class KVCacheManager:
         (reference cache_manager.py:509-546)."""
         B = len(seq_ids)
         if B > 0:
+            if self._updates_pending:
+                # the full table below supersedes an update list nobody applied; left in place it would later be
+                # written over rows of a DIFFERENT batch layout
+                self._updates_dev[:1].zero_()
+                self._updates_pending = False
             stage = self._stages[self._stage_idx]
             self._stage_idx ^= 1
             if stage["event"] is not None:
@@ -224,21 +230,44 @@ class KVCacheManager:
         launch of a multi-step decode graph).  Rows must already be laid out by ``cache_batch_data`` in this order.
         Returns the number of new pages; -1 if the pool ran dry (like ``append``)."""
         assert self._on_gpu, "append_on_device: CUDA cache manager only"
-        ups = []
-        for row, sid in enumerate(seq_ids):
+        # Dry run first: nothing below may fail after the host allocator has moved, or pages handed to earlier rows
+        # would never reach the device table.  A page holds block_size - 1 appended tokens (the reference's offset
+        # quirk, see ``append``); a fresh page starts at position 1.
+        per_page = self.block_size - 1
+        need = 0
+        for sid in seq_ids:
             blocks = self._blocks.get(sid)
             if blocks is None:
                 return -1
-            before = len(blocks)
-            for _ in range(steps):
-                if self.append(sid) < 0:
-                    return -1
-            for col in range(before, len(blocks)):
-                if col >= self.max_seq_blocks:
-                    raise ValueError("sequence outgrew the block table")
+            room = per_page - self._pos[blocks[-1]]
+            new_pages = 0 if steps <= room else -(-(steps - room) // per_page)
+            if len(blocks) + new_pages > self.max_seq_blocks:
+                raise ValueError("sequence outgrew the block table")
+            need += new_pages
+        if need > len(self._free):
+            print(f"cache_manager.append_on_device failed: {need} pages needed for {steps} steps, free={len(self._free)}")
+            return -1
+        if need > self.max_table_updates:
+            raise ValueError(f"{need} new pages exceed the device update list ({self.max_table_updates} entries); use fewer steps")
+        if need and self._updates_pending:
+            raise RuntimeError("append_on_device: the previous update list has not been applied on the device yet "
+                               "(advance_lengths or a multi-step graph replay consumes it); a second upload would "
+                               "overwrite pages the device block table never received")
+        # step-major like the engine (engine.py:248-262: every step appends to each sequence in batch order), so the
+        # free list hands the same page to the same sequence as K single steps would
+        before = [len(self._blocks[sid]) for sid in seq_ids]
+        for _ in range(steps):
+            for sid in seq_ids:
+                got = self.append(sid)
+                assert got >= 0, "append_on_device: the dry run admitted a request the allocator refused"
+        ups = []
+        for row, sid in enumerate(seq_ids):
+            blocks = self._blocks[sid]
+            for col in range(before[row], len(blocks)):
                 ups.append((row, col, blocks[col]))
+        assert len(ups) == need
         if ups:
-            assert len(ups) <= self.max_table_updates, "too many new pages for one update list"
+            self._updates_pending = True
             st = self._upd_stages[self._upd_idx]
             self._upd_idx ^= 1
             if st["event"] is not None:
@@ -255,6 +284,12 @@ class KVCacheManager:
         """``cache_seqlens[:B] += delta`` and apply pending table updates, on the device (one tiny launch)."""
         import b200ops
         b200ops.table_advance(self._cache_seqlens_buffer, batch_size, delta, self._block_table_buffer, self._updates_dev)
+        self._updates_pending = False
+
+    def mark_updates_applied(self) -> None:
+        """Tell the host side that a launch outside this class (the first node of a multi-step decode graph) has been
+        enqueued behind the upload and consumes the update list."""
+        self._updates_pending = False
 
     def get_buffer_data(self, seq_ids: list):
         B = len(seq_ids)

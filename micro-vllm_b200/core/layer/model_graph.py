@@ -47,6 +47,35 @@ from .rope import RoPE
 logger = logging.getLogger(__name__)
 
 
+def select_ar_mode(want: str, world_size: int, has_multicast: bool, ln_f_kernel_norm: bool, max_rows: int) -> str:
+    """Form of the fused all-reduce + residual + RMSNorm the decode step uses (``B200_AR_MODE``, default "auto").
+
+    ``ln_f_kernel_norm``: the model's final norm is a kernel norm, so EVERY reduction of the step is followed by a norm
+    this library runs.  The last layer's reduction of a model whose ``ln_f`` is a plain module carries no norm
+    (weight = None), and only the one-shot peer-load form accepts that: "sharded", "ll" and all NVLS forms (one-hop
+    included — ``b200_allreduce_residual_rmsnorm`` refuses them without a weight) need the norm, so such a model always
+    gets "oneshot".  The owner-rank forms ("sharded", "ll", "nvls", "nvlsp": each row reduced and normalised on ONE
+    rank) are further limited to ``max_rows`` <= 1024; the one-hop form "nvls1" keeps the one-shot contract.
+
+    Measured (profiles/r02/allreduce_tp{2,8}.json, 64 x 8192 bf16): 2 ranks — peer-load one-shot 7.0 us, one-hop NVLS
+    9.2, two-hop NVLS 13.4, NCCL 19.1; 8 ranks — two-hop NVLS 13.5 us, one-hop NVLS 18.0 (every rank pulls the whole
+    tensor through the switch: 8 MB leave each GPU), one-shot 21.7, LL 33.5, NCCL 34.1.  Whole L70-shaped step at
+    TP = 8: 2.56 / 2.72 / 2.84 / 3.20 ms (nvls / nvls1 / oneshot / ll)."""
+    if not ln_f_kernel_norm:
+        return "oneshot"
+    owner_ok = max_rows <= 1024
+    if want == "auto":
+        if world_size >= 4:
+            want = ("nvls" if owner_ok else "nvls1") if has_multicast else "ll"
+        else:
+            want = "oneshot"
+    if want in ("nvls", "nvls1", "nvlsp") and not has_multicast:
+        want = "ll" if world_size >= 4 else "oneshot"
+    if want == "nvls1" or (want in ("ll", "sharded", "nvls", "nvlsp") and owner_ok):
+        return want
+    return "oneshot"
+
+
 class ModelGraphRunner:
     def __init__(self, model, num_layers: int, num_heads: int, head_size: int,
                  kv_num_heads: int, hidden_dim: int, intermediate_size: int,
@@ -112,7 +141,7 @@ class ModelGraphRunner:
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self._graphs_balanced: Dict[int, torch.cuda.CUDAGraph] = {}
         self._graphs_multi: Dict[tuple, torch.cuda.CUDAGraph] = {}
-        self._tok_hist = None
+        self._tok_hists = {}                # (bs, steps) -> id history buffer owned by that multi-step graph
         self._is_graph_ready = False
 
     # ------------------------------------------------------------------ init
@@ -209,22 +238,8 @@ class ModelGraphRunner:
             self._attn_out = self._comm.slot(0, mb, self.hidden_dim)
             self._mlp_out = self._comm.slot(1, mb, self.hidden_dim)
             want = os.environ.get("B200_AR_MODE", "auto")
-            fusable = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False)) and mb <= 1024
-            if want == "auto":
-                # measured (profiles/r02/allreduce_tp{2,8}.json, 64 x 8192 bf16): 2 ranks — peer-load one-shot 7.0 us,
-                # one-hop NVLS 9.2, two-hop NVLS 13.4, NCCL 19.1; 8 ranks — two-hop NVLS 13.5 us, one-hop NVLS 18.0 (every
-                # rank pulls the whole tensor through the switch: 8 MB leave each GPU), one-shot 21.7, LL 33.5, NCCL 34.1.
-                # Whole L70-shaped step at TP = 8: 2.56 / 2.72 / 2.84 / 3.20 ms (nvls / nvls1 / oneshot / ll).
-                if self.world_size >= 4:
-                    want = ("nvls" if fusable else "nvls1") if self._comm.has_multicast else "ll"
-                else:
-                    want = "oneshot"
-            if want in ("nvls", "nvls1", "nvlsp") and not self._comm.has_multicast:
-                want = "ll" if self.world_size >= 4 else "oneshot"
-            if want in ("ll", "sharded", "nvls", "nvlsp") and fusable:
-                self._ar_mode = want
-            if want == "nvls1":                         # one-hop in-switch form: the one-shot contract, no ln_f condition
-                self._ar_mode = want
+            kernel_ln_f = bool(getattr(self.model.transformer.ln_f, "b200_kernel_norm", False))
+            self._ar_mode = select_ar_mode(want, self.world_size, self._comm.has_multicast, kernel_ln_f, mb)
             if self._ar_mode in ("sharded", "nvls"):
                 self._normed = self._comm.ybuf(mb, self.hidden_dim)
         self._zero_table = torch.zeros((mb, self.attention.max_blocks), dtype=torch.int32, device=dev)
@@ -481,8 +496,9 @@ class ModelGraphRunner:
         key = (bs, steps)
         if key in self._graphs_multi:
             return
-        if self._tok_hist is None or self._tok_hist.shape[0] < steps:
-            self._tok_hist = torch.zeros((max(steps, 16), self.max_bs), dtype=torch.long, device=self.device)
+        # one history buffer per captured graph, kept for the graph's lifetime: a graph holds raw addresses, so a
+        # buffer it writes must never be replaced (and freed) when a later capture needs more rows
+        hist = torch.zeros((steps, bs), dtype=torch.long, device=self.device)
         seqlens, table = cache_manager._cache_seqlens_buffer, cache_manager._block_table_buffer
         dummy = torch.randint(0, self.vocab_size, (bs,), device=self.device)
         with torch.no_grad():
@@ -498,10 +514,11 @@ class ModelGraphRunner:
                 if lg.data_ptr() != self._logits.data_ptr():
                     self._logits[:bs] = lg
                 b200ops.greedy_argmax(self._logits[:bs], self._next_ids[:bs])
-                self._tok_hist[s, :bs].copy_(self._next_ids[:bs])
+                hist[s].copy_(self._next_ids[:bs])
                 self._input_ids[:bs].copy_(self._next_ids[:bs])
                 b200ops.table_advance(seqlens, bs, 1)              # the token just cached is part of the context now
         self._graphs_multi[key] = g
+        self._tok_hists[key] = hist
 
     def forward_greedy_multistep(self, input_ids: torch.Tensor, cache_manager, seq_ids: list, steps: int) -> torch.Tensor:
         """``steps`` greedy decode steps for the sequences ``seq_ids`` (rows of the batch in this order, lengths and
@@ -518,7 +535,8 @@ class ModelGraphRunner:
             raise RuntimeError("OOM: KV cache pool exhausted")           # engine.py:220 convention
         self._input_ids[:bs] = input_ids
         self._graphs_multi[key].replay()
-        return self._tok_hist[:steps, :bs].t()
+        cache_manager.mark_updates_applied()                 # the graph's first node consumed the update list
+        return self._tok_hists[key].t()
 
     def forward_greedy(self, input_ids: torch.Tensor, cache_manager, batch_size: int) -> torch.Tensor:
         """One decode step returning the greedy next-token ids ``[batch_size]`` int64 (a view of a static

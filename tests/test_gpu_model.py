@@ -293,3 +293,120 @@ def test_multistep_greedy_graph_matches_single_steps():
         for s_ in ids:
             orc.append(s_)
     assert orc.snapshot() == {"free": state_single[0], "blocks": state_single[1], "pos": state_single[2]}
+
+
+def test_multistep_graphs_of_different_lengths_keep_their_own_history():
+    """A multi-step graph captured EARLIER must still return fresh ids after a LONGER one was captured: each graph owns
+    the id-history buffer it writes (a shared buffer regrown by the later capture would leave the first graph writing
+    into released memory and the caller reading stale ids).  K = 4, then K = 20 (> the old 16-row default), then the
+    K = 4 graph again, all against engine-style single steps."""
+    shape = SHAPES["qwen2.5-0.5b"]
+    L, P, B = 2, 100, 2
+    plan = [4, 20, 4, 20]
+    model, dec, pre, mgr = make_runners(shape, L, max_bs=B, seed=5, std=0.01, peaky=True, vocab=8192)
+    g = torch.Generator().manual_seed(11)
+    prompt = torch.randint(0, 8192, (B, P), generator=g)
+    ids = list(range(B))
+
+    def prefill():
+        mgr.reset()
+        for lyr in range(L):
+            mgr.k_caches[lyr].zero_()
+            mgr.v_caches[lyr].zero_()
+        for s_ in ids:
+            assert mgr.alloc(s_, P)[0]
+        mgr.cache_batch_data(ids, [P] * B)
+        with torch.no_grad():
+            logits = pre.forward(prompt.cuda(), mgr, B)
+        return logits[:, -1, :].float().argmax(-1)
+
+    dec.capture(mgr, batch_sizes=[B], greedy=True)
+    tok = prefill()
+    single, pos = [], P + 1
+    for _ in range(sum(plan)):
+        for s_ in ids:
+            mgr.append(s_)
+        mgr.cache_batch_data(ids, [pos] * B)
+        tok = dec.forward_greedy(tok, mgr, B).clone()
+        single.append(tok.cpu())
+        pos += 1
+    single = torch.stack(single, 1)
+    tok = prefill()
+    mgr.cache_batch_data(ids, [P + 1] * B)
+    multi = []
+    for K in plan:
+        out = dec.forward_greedy_multistep(tok, mgr, ids, K)
+        assert out.shape == (B, K)
+        multi.append(out.cpu())
+        tok = out[:, -1].clone()
+    torch.cuda.synchronize()
+    assert torch.cat(multi, 1).tolist() == single.tolist()
+    assert len(dec._tok_hists) == 2 and dec._tok_hists[(B, 4)].data_ptr() != dec._tok_hists[(B, 20)].data_ptr()
+
+
+def test_append_on_device_is_all_or_nothing_and_guards_its_update_list():
+    """KVCacheManager.append_on_device: (1) same allocator state and device table as K x append + cache_batch_data;
+    (2) a request the pool or the update list cannot take leaves the host allocator untouched (a half-done batch
+    would own pages the device table never hears about); (3) a second page-producing call before the first list was
+    applied is refused instead of overwriting it; (4) cache_batch_data cancels a list it supersedes."""
+    from core.cache_manager import KVCacheManager
+
+    def mk(n_blocks=8):
+        return KVCacheManager(n_blocks, 256, 1, 1, 8, dtype=torch.bfloat16, device="cuda", max_tokens=1024, max_batch_size=2)
+
+    def state(m):
+        return (list(m._free), {k: list(v) for k, v in m._blocks.items()}, dict(m._pos))
+
+    # (1) 300 steps from lengths 250 / 10: rows cross one and two page boundaries (a page takes 255 appended tokens)
+    a, b = mk(), mk()
+    for m in (a, b):
+        assert m.alloc(0, 250)[0] and m.alloc(1, 10)[0]
+        m.cache_batch_data([0, 1], [251, 11])
+    for _ in range(300):
+        a.append(0), a.append(1)
+    assert b.append_on_device([0, 1], 300) == 3
+    assert state(a) == state(b)
+    b.advance_lengths(2, 300)
+    want_bt, _ = a.cache_batch_data([0, 1], [551, 311])
+    torch.cuda.synchronize()
+    assert torch.equal(b._block_table_buffer[:2], want_bt)
+    assert b._cache_seqlens_buffer[:2].tolist() == [551, 311]
+    assert int(b._updates_dev[0]) == 0 and not b._updates_pending
+    # (2) pool too small for the whole batch: -1 and nothing moved (row 0 alone would have fitted)
+    c = mk(n_blocks=3)
+    assert c.alloc(0, 250)[0] and c.alloc(1, 250)[0]
+    c.cache_batch_data([0, 1], [251, 251])
+    before = state(c)
+    assert c.append_on_device([0, 1], 20) == -1
+    assert state(c) == before and not c._updates_pending
+    assert c.append_on_device([0, 7], 1) == -1 and state(c) == before          # unknown sequence
+    with pytest.raises(ValueError):                                              # 5 pages > the 4-column table (1024 tokens)
+        _outgrow(mk(n_blocks=16))
+    # (3) pending list
+    d = mk()
+    assert d.alloc(0, 250)[0] and d.alloc(1, 250)[0]
+    d.cache_batch_data([0, 1], [251, 251])
+    assert d.append_on_device([0, 1], 10) == 2 and d._updates_pending
+    assert d.append_on_device([0, 1], 10) == 0                                   # no new page: nothing to overwrite
+    before = state(d)
+    with pytest.raises(RuntimeError):
+        d.append_on_device([0, 1], 300)
+    assert state(d) == before
+    d.advance_lengths(2, 20)
+    assert d.append_on_device([0, 1], 300) == 2
+    # (4) a full upload supersedes the list
+    d.cache_batch_data([1, 0], [571, 571])
+    assert not d._updates_pending
+    torch.cuda.synchronize()
+    assert int(d._updates_dev[0]) == 0
+    assert d._block_table_buffer[:2, :3].tolist() == [d._blocks[1][:3], d._blocks[0][:3]]
+
+
+def _outgrow(m):
+    assert m.alloc(0, 1000)[0]
+    m.cache_batch_data([0], [1001])
+    before = (list(m._free), {k: list(v) for k, v in m._blocks.items()}, dict(m._pos))
+    try:
+        m.append_on_device([0], 200)
+    finally:
+        assert (list(m._free), {k: list(v) for k, v in m._blocks.items()}, dict(m._pos)) == before

@@ -114,3 +114,24 @@ def test_single_process_defaults():
         for k, v in env.items():
             if v is not None:
                 os.environ[k] = v
+
+
+def test_reduction_form_selection_respects_a_plain_final_norm():
+    """A model whose ln_f is a plain module sends weight=None with the last layer's reduction; only the one-shot form
+    accepts that (b200_allreduce_residual_rmsnorm refuses every NVLS / LL / sharded call without a norm), so such a
+    model must never be given another form, whatever the node offers or B200_AR_MODE asks for."""
+    from core.layer.model_graph import select_ar_mode
+    for want in ("auto", "nvls", "nvls1", "nvlsp", "ll", "sharded", "oneshot"):
+        for world in (2, 4, 8):
+            for mc in (False, True):
+                assert select_ar_mode(want, world, mc, False, 64) == "oneshot"
+    # kernel ln_f: the measured defaults
+    assert select_ar_mode("auto", 8, True, True, 64) == "nvls"
+    assert select_ar_mode("auto", 4, False, True, 64) == "ll"
+    assert select_ar_mode("auto", 2, True, True, 64) == "oneshot"
+    assert select_ar_mode("auto", 8, True, True, 2048) == "nvls1"        # owner-rank forms stop at 1024 rows
+    assert select_ar_mode("nvls1", 8, True, True, 2048) == "nvls1"
+    assert select_ar_mode("nvls", 8, True, True, 2048) == "oneshot"
+    assert select_ar_mode("nvls", 8, False, True, 64) == "ll"            # no multicast range: packet form
+    assert select_ar_mode("nvls1", 2, False, True, 64) == "oneshot"
+    assert select_ar_mode("bogus", 8, True, True, 64) == "oneshot"
