@@ -75,7 +75,6 @@ AR_MODE_NVLS = 4
 AR_MODE_NVLS_ONEHOP = 8
 AR_FLAG_PDL = 0x100
 AR_FLAG_PACKET_TAIL = 0x200
-AR_FLAG_PDL = 0x100
 AR_NVLS_READY_WORD = AR_MAX_CTAS * (AR_MAX_WORLD + 1)
 AR_NVLS_DONE_WORD = AR_NVLS_READY_WORD + 32
 
