@@ -564,6 +564,34 @@ def run_b200_arm(args):
     d2h = world * out_host.numel() * 2
     splits_used = num_splits or b200ops.decode_num_splits(B, Hkv_l, per_seq * page, b200ops.sm_count(dev))
 
+    # ---- the reference's own GPU operator on the SAME workload, same caches, same graph-replay timing:
+    # flash_attn_with_kvcache called as /root/reference core/layer/model_graph.py:161-168 calls it, including its
+    # num_splits = max(1, 32 // (4 * bs)).  Context for the headline, never part of `value`; library code, not ours.
+    ref_op = None
+    if rank == 0 and not args.no_configs:
+        try:
+            from flash_attn import flash_attn_with_kvcache as fa
+            fa_splits = max(1, 32 // (4 * B))
+
+            def fa_layers():
+                x_all = qkv_devs[0]
+                for l in range(L):
+                    x = x_all[l]
+                    fa(x[:, : Hq_l * D].view(B, 1, Hq_l, D), mgr.k_caches[l], mgr.v_caches[l],
+                       k=x[:, Hq_l * D: (Hq_l + Hkv_l) * D].view(B, 1, Hkv_l, D),
+                       v=x[:, (Hq_l + Hkv_l) * D:].view(B, 1, Hkv_l, D), rotary_cos=cos, rotary_sin=sin,
+                       cache_seqlens=seqlens, block_table=block_table, causal=True, rotary_interleaved=False,
+                       num_splits=fa_splits)
+            fa_ms = _time_graph(_graph_of(fa_layers), reps=max(3, min(args.steps, 10)))
+            ref_op = {"operator": "flash_attn 2.8.3 flash_attn_with_kvcache (the reference's decode call, model_graph.py:161-168)",
+                      "num_splits": fa_splits, "ms_per_step": round(fa_ms, 4), "us_per_call": round(fa_ms * 1e3 / L, 2),
+                      "kv_GBps": round(bytes_step / world / (fa_ms * 1e-3) / 1e9, 1),
+                      "b200_kernel_us_per_call": round(kernel_us, 2), "ratio_us": round(fa_ms * 1e3 / L / kernel_us, 3),
+                      "timing": "CUDA graph of the step's launches, CUDA events, this rank's shard"}
+            del fa_layers
+        except Exception as e:  # noqa: BLE001 - context figure only
+            ref_op = {"error": f"{type(e).__name__}: {e}"[:200]}
+
     # ---- free the headline's memory before the auxiliary figures
     del graph, chunk_graphs, mgr, qkv_dev, out_dev, qkv_devs, out_devs, out_views, qkv_host, out_host, block_table, seqlens
     _release()
@@ -668,6 +696,7 @@ def run_b200_arm(args):
         "gpu_launches": args.steps * L,
         "clocks": clk.summary(),
         "tokens_per_s_attention_only": round(B / (ms_step * 1e-3), 1),
+        "reference_gpu_operator": ref_op,
         "decode_step": step,
         "tp_check": tp_check,
         "decode_step_l8": step_l8,
