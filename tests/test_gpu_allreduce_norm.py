@@ -505,10 +505,14 @@ def _peer_worker(rank, world, port, q):
         q.put((rank, "FAIL: " + traceback.format_exc()))
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (NVLink peer memory)")
-def test_peer_memory_allreduce_two_processes():
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_peer_memory_allreduce_one_process_per_gpu(world):
+    """Every reduction form and the column all-gather on REAL peers (NVLink peer memory, NVSwitch multicast when the
+    node has it) against the oracle, eager and through CUDA-graph replays; 4 and 8 ranks are where the in-switch forms
+    are the decode runner's default.  Skipped on boxes with fewer GPUs (logs of the 2 / 4 / 8-GPU runs: profiles/r03/)."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs >= {world} GPUs (NVLink peer memory)")
     import torch.multiprocessing as mp
-    world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()

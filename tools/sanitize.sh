@@ -1,6 +1,7 @@
 #!/usr/bin/env bash
 # Race / memory checks of the hand-written kernels on small shapes (SURVEY.md §5 "race detection").
-# GPU box only:  gpurun --timeout 1500 -- 'bash tools/sanitize.sh'
+# GPU box only:  gpurun --timeout 1500 -- 'bash tools/sanitize.sh'   (round 3: the B200 pool refuses compute-sanitizer
+# outright, every leg returned rc=86 with the pool's notice)
 # Each leg runs under its own `timeout`; logs and a one-line-per-leg summary land in gpurun_out/sanitizer/.
 # What is covered: smoke() (split-KV decode with the cluster/DSMEM merge, tcgen05 prefill, RMSNorm, SwiGLU, arg-max,
 # split-K GEMM) and a selection of the smallest parity tests of every file (balanced stream-K decode, store_kvcache,
